@@ -1,0 +1,311 @@
+// nccl_probe.cu — the NVLink health probe: an NCCL fp32 sum all-reduce sweep (SURVEY.md §8 a10,
+// §8d cfg4).  This is the only place the library touches NCCL, and it does so through dlopen so
+// that libb200validate.so loads (and validates a GPU) on images that ship no NCCL at all.
+//
+// Inputs are integer-valued floats — rank r holds (float)((i*(2r+1) + r) & 15) — so the reduced value is
+// exact whatever order the ring, tree or NVSwitch reduction adds in, and the result is checked
+// bit for bit against the closed form on the device.
+#include <algorithm>
+#include <cstring>
+#include <dlfcn.h>
+#include <mutex>
+#include <nccl.h>   // types and enums only; every function is resolved with dlsym
+#include <vector>
+
+#include "common.cuh"
+
+namespace b200v {
+namespace {
+
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetVersion)(int *) = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+};
+
+NcclApi g_nccl;
+std::once_flag g_nccl_once;
+int g_last_nccl = 0;
+
+template <typename F>
+bool sym(void *h, const char *name, F &out) {
+    out = reinterpret_cast<F>(dlsym(h, name));
+    return out != nullptr;
+}
+
+const NcclApi *nccl() {
+    std::call_once(g_nccl_once, [] {
+        void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return;
+        NcclApi a;
+        a.handle = h;
+        bool ok = sym(h, "ncclGetVersion", a.GetVersion) && sym(h, "ncclGetUniqueId", a.GetUniqueId) &&
+                  sym(h, "ncclCommInitRank", a.CommInitRank) && sym(h, "ncclCommInitAll", a.CommInitAll) &&
+                  sym(h, "ncclCommDestroy", a.CommDestroy) && sym(h, "ncclAllReduce", a.AllReduce) &&
+                  sym(h, "ncclGroupStart", a.GroupStart) && sym(h, "ncclGroupEnd", a.GroupEnd);
+        if (ok) g_nccl = a;
+    });
+    return g_nccl.handle ? &g_nccl : nullptr;
+}
+
+#define B200V_NCCL(expr, rowptr)                                  \
+    do {                                                          \
+        ncclResult_t r__ = (expr);                                \
+        if (r__ != ncclSuccess) {                                 \
+            g_last_nccl = (int)r__;                               \
+            if (rowptr) (rowptr)->nccl_result = (int)r__;         \
+            return B200V_E_NCCL;                                  \
+        }                                                         \
+    } while (0)
+
+// (i+r)&7 would do for 2 and 4 ranks but sums to the constant 28 over 8 ranks; the odd multiplier
+// keeps the sum a function of i at every rank count.  Sums stay below 2^24, hence exact.
+__host__ __device__ inline float ar_value(size_t i, int r) {
+    return (float)((i * (size_t)(2 * r + 1) + (size_t)r) & 15);
+}
+
+__global__ void __launch_bounds__(256) ar_fill_kernel(float *buf, size_t n, int rank) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockDim.x * blockIdx.x + threadIdx.x; i < n; i += stride)
+        buf[i] = ar_value(i, rank);
+}
+
+// Counts elements whose bits differ from sum_{r<nranks} ar_value(i, r).
+__global__ void __launch_bounds__(256)
+ar_check_kernel(const float *buf, size_t n, int nranks, unsigned long long *bad) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    unsigned long long local = 0;
+    for (size_t i = (size_t)blockDim.x * blockIdx.x + threadIdx.x; i < n; i += stride) {
+        float want = 0.0f;
+        for (int r = 0; r < nranks; ++r) want += ar_value(i, r);
+        local += __float_as_uint(want) != __float_as_uint(buf[i]);
+    }
+    if (local) atomicAdd(bad, local);
+}
+
+struct Rank {
+    int dev = -1, rank = -1;
+    ncclComm_t comm = nullptr;
+    cudaStream_t st = nullptr;
+    float *buf = nullptr;
+    unsigned long long *d_bad = nullptr;
+    int sm_count = 0;
+    std::vector<cudaEvent_t> ev;
+};
+
+void destroy_ranks(const NcclApi *api, std::vector<Rank> &rs) {
+    for (Rank &r : rs) {
+        if (r.dev < 0) continue;
+        cudaSetDevice(r.dev);
+        if (r.st) cudaStreamSynchronize(r.st);
+        if (r.comm) api->CommDestroy(r.comm);
+        for (cudaEvent_t e : r.ev) cudaEventDestroy(e);
+        if (r.buf) cudaFree(r.buf);
+        if (r.d_bad) cudaFree(r.d_bad);
+        if (r.st) cudaStreamDestroy(r.st);
+    }
+    rs.clear();
+}
+
+int setup_rank(Rank &r, size_t max_bytes, int iters) {
+    B200V_CUDA(cudaSetDevice(r.dev));
+    B200V_CUDA(cudaDeviceGetAttribute(&r.sm_count, cudaDevAttrMultiProcessorCount, r.dev));
+    B200V_CUDA(cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+    B200V_CUDA(cudaMalloc(&r.buf, max_bytes));
+    B200V_CUDA(cudaMalloc(&r.d_bad, 8));
+    r.ev.resize((size_t)iters * 2);
+    for (auto &e : r.ev) B200V_CUDA(cudaEventCreate(&e));
+    return B200V_OK;
+}
+
+int grid_for(const Rank &r, size_t n) {
+    size_t g = (n + 255) / 256;
+    const size_t cap = (size_t)r.sm_count * 8;
+    if (g > cap) g = cap;
+    return g < 1 ? 1 : (int)g;
+}
+
+// One all-reduce across the local ranks, grouped when this process drives more than one device.
+int allreduce_once(const NcclApi *api, std::vector<Rank> &rs, size_t count, b200v_ar_row *row) {
+    if (rs.size() > 1) B200V_NCCL(api->GroupStart(), row);
+    for (Rank &r : rs) {
+        B200V_CUDA(cudaSetDevice(r.dev));
+        B200V_NCCL(api->AllReduce(r.buf, r.buf, count, ncclFloat, ncclSum, r.comm, r.st), row);
+    }
+    if (rs.size() > 1) B200V_NCCL(api->GroupEnd(), row);
+    return B200V_OK;
+}
+
+int sweep(const NcclApi *api, std::vector<Rank> &rs, int nranks, size_t min_bytes, size_t max_bytes,
+          int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows) {
+    int nr = 0;
+    for (size_t bytes = min_bytes; bytes <= max_bytes && nr < max_rows; bytes *= 2) {
+        b200v_ar_row *row = &rows[nr];
+        std::memset(row, 0, sizeof(*row));
+        row->bytes = bytes;
+        const size_t count = bytes / 4;
+
+        // correctness pass: fill, one all-reduce, bitwise check against the closed form
+        for (Rank &r : rs) {
+            B200V_CUDA(cudaSetDevice(r.dev));
+            ar_fill_kernel<<<grid_for(r, count), 256, 0, r.st>>>(r.buf, count, r.rank);
+            B200V_CUDA(cudaGetLastError());
+            B200V_CUDA(cudaMemsetAsync(r.d_bad, 0, 8, r.st));
+        }
+        int rc = allreduce_once(api, rs, count, row);
+        if (rc != B200V_OK) return rc;
+        for (Rank &r : rs) {
+            B200V_CUDA(cudaSetDevice(r.dev));
+            ar_check_kernel<<<grid_for(r, count), 256, 0, r.st>>>(r.buf, count, nranks, r.d_bad);
+            B200V_CUDA(cudaGetLastError());
+            unsigned long long bad = 0;
+            B200V_CUDA(cudaMemcpyAsync(&bad, r.d_bad, 8, cudaMemcpyDeviceToHost, r.st));
+            B200V_CUDA(cudaStreamSynchronize(r.st));
+            row->mismatches += bad;
+        }
+
+        // timing pass (values keep accumulating in place; they are not read again)
+        for (int i = 0; i < warmup; ++i) {
+            rc = allreduce_once(api, rs, count, row);
+            if (rc != B200V_OK) return rc;
+        }
+        for (int i = 0; i < iters; ++i) {
+            for (Rank &r : rs) {
+                B200V_CUDA(cudaSetDevice(r.dev));
+                B200V_CUDA(cudaEventRecord(r.ev[2 * i], r.st));
+            }
+            rc = allreduce_once(api, rs, count, row);
+            if (rc != B200V_OK) return rc;
+            for (Rank &r : rs) {
+                B200V_CUDA(cudaSetDevice(r.dev));
+                B200V_CUDA(cudaEventRecord(r.ev[2 * i + 1], r.st));
+            }
+        }
+        for (Rank &r : rs) {
+            B200V_CUDA(cudaSetDevice(r.dev));
+            B200V_CUDA(cudaStreamSynchronize(r.st));
+        }
+        std::vector<float> ms((size_t)iters, 0.f);
+        for (int i = 0; i < iters; ++i)
+            for (Rank &r : rs) {
+                float t = 0.f;
+                B200V_CUDA(cudaEventElapsedTime(&t, r.ev[2 * i], r.ev[2 * i + 1]));
+                ms[i] = std::max(ms[i], t);   // max over the ranks this process drives
+            }
+        std::sort(ms.begin(), ms.end());
+        row->best_ms = ms[0];
+        row->median_ms = ms[(size_t)iters / 2];
+        row->algbw_gbs = (double)bytes / (row->best_ms * 1e-3) / 1e9;
+        row->busbw_gbs = row->algbw_gbs * 2.0 * (nranks - 1) / nranks;
+        ++nr;
+        if (bytes > max_bytes / 2) break;   // next doubling would overflow or pass max
+    }
+    *nrows = nr;
+    return B200V_OK;
+}
+
+bool bad_sweep_args(size_t min_bytes, size_t max_bytes, int warmup, int iters, const void *rows,
+                    int max_rows, const int *nrows) {
+    return !rows || !nrows || max_rows < 1 || iters < 1 || warmup < 0 || min_bytes < 4 ||
+           (min_bytes & 3) || max_bytes < min_bytes;
+}
+
+}  // namespace
+}  // namespace b200v
+
+using namespace b200v;
+
+extern "C" {
+
+int b200v_nccl_version(int *version) {
+    if (!version) return B200V_E_BADARG;
+    const NcclApi *api = nccl();
+    if (!api) return B200V_E_NONCCL;
+    B200V_NCCL(api->GetVersion(version), (b200v_ar_row *)nullptr);
+    return B200V_OK;
+}
+
+int b200v_last_nccl_error(void) { return g_last_nccl; }
+
+int b200v_nccl_unique_id(unsigned char id[B200V_NCCL_UNIQUE_ID_BYTES]) {
+    static_assert(sizeof(ncclUniqueId) == B200V_NCCL_UNIQUE_ID_BYTES, "ncclUniqueId is 128 bytes");
+    if (!id) return B200V_E_BADARG;
+    const NcclApi *api = nccl();
+    if (!api) return B200V_E_NONCCL;
+    ncclUniqueId u;
+    B200V_NCCL(api->GetUniqueId(&u), (b200v_ar_row *)nullptr);
+    std::memcpy(id, &u, sizeof(u));
+    return B200V_OK;
+}
+
+int b200v_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes, int warmup,
+                          int iters, b200v_ar_row *rows, int max_rows, int *nrows) {
+    if (ndev < 1 || !devs || bad_sweep_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
+        return B200V_E_BADARG;
+    *nrows = 0;
+    int count = 0;
+    int rc = b200v_device_count(&count);
+    if (rc != B200V_OK) return rc;
+    for (int i = 0; i < ndev; ++i)
+        if (devs[i] < 0 || devs[i] >= count) return B200V_E_BADARG;
+    const NcclApi *api = nccl();
+    if (!api) return B200V_E_NONCCL;
+
+    std::vector<Rank> rs((size_t)ndev);
+    struct Cleanup {
+        const NcclApi *api;
+        std::vector<Rank> &rs;
+        ~Cleanup() { destroy_ranks(api, rs); }
+    } cleanup{api, rs};
+    for (int i = 0; i < ndev; ++i) {
+        rs[i].dev = devs[i];
+        rs[i].rank = i;
+        rc = setup_rank(rs[i], max_bytes, iters);
+        if (rc != B200V_OK) return rc;
+    }
+    std::vector<ncclComm_t> comms((size_t)ndev);
+    B200V_NCCL(api->CommInitAll(comms.data(), ndev, devs), (b200v_ar_row *)nullptr);
+    for (int i = 0; i < ndev; ++i) rs[i].comm = comms[i];
+    return sweep(api, rs, ndev, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
+}
+
+int b200v_allreduce_probe_rank(int dev, int rank, int nranks,
+                               const unsigned char id[B200V_NCCL_UNIQUE_ID_BYTES], size_t min_bytes,
+                               size_t max_bytes, int warmup, int iters, b200v_ar_row *rows,
+                               int max_rows, int *nrows) {
+    if (!id || nranks < 1 || rank < 0 || rank >= nranks ||
+        bad_sweep_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
+        return B200V_E_BADARG;
+    *nrows = 0;
+    int count = 0;
+    int rc = b200v_device_count(&count);
+    if (rc != B200V_OK) return rc;
+    if (dev < 0 || dev >= count) return B200V_E_BADARG;
+    const NcclApi *api = nccl();
+    if (!api) return B200V_E_NONCCL;
+
+    std::vector<Rank> rs(1);
+    struct Cleanup {
+        const NcclApi *api;
+        std::vector<Rank> &rs;
+        ~Cleanup() { destroy_ranks(api, rs); }
+    } cleanup{api, rs};
+    rs[0].dev = dev;
+    rs[0].rank = rank;
+    rc = setup_rank(rs[0], max_bytes, iters);
+    if (rc != B200V_OK) return rc;
+    ncclUniqueId u;
+    std::memcpy(&u, id, sizeof(u));
+    B200V_NCCL(api->CommInitRank(&rs[0].comm, nranks, u, rank), (b200v_ar_row *)nullptr);
+    return sweep(api, rs, nranks, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
+}
+
+}  // extern "C"
