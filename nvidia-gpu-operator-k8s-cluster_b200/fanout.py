@@ -33,3 +33,39 @@ def status_file_names(ndev):
     """Status files the fan-out leaves under OUTPUT_DIR on success: one per GPU
     and cuda-ready only when every GPU passed.  All match upstream's preStop `rm -f *-ready`."""
     return ["cuda-gpu%d-ready" % i for i in range(ndev)] + ["cuda-ready"]
+
+
+# ---- cross-rank folding (torch.distributed is plumbing only: a barrier and two reductions) -------
+
+def _dist():
+    import torch.distributed as dist
+    return dist if (dist.is_available() and dist.is_initialized()) else None
+
+
+def max_over_ranks(value, device="cpu"):
+    """Max of a per-rank scalar over all ranks (the slowest rank's time).  Identity when
+    torch.distributed is not initialised."""
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1:
+        return float(value)
+    import torch
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value, device="cpu"):
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1:
+        return float(value)
+    import torch
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def job_throughput_gbs(bytes_this_rank, seconds_this_rank, device="cpu"):
+    """Whole-job GB/s from per-rank figures: all ranks' bytes over the slowest rank's time."""
+    total = sum_over_ranks(bytes_this_rank, device)
+    slowest = max_over_ranks(seconds_this_rank, device)
+    return aggregate_gbs([total], slowest)

@@ -1,0 +1,489 @@
+// validator_core.cpp — see validator_core.h.  Plain C++17 + POSIX; no CUDA headers here: the GPU is
+// reached only through the Api table (the C ABI of include/b200validate.h).
+#include "validator_core.h"
+
+#include <cerrno>
+#include <cinttypes>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <dirent.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
+
+namespace b200v_host {
+
+namespace {
+
+const char *kOpNames[B200V_OP_COUNT] = {"copy", "scale", "add", "triad", "vectoradd", "triad_unfused"};
+
+std::string env_or(const char *name, const std::string &dflt) {
+    const char *v = std::getenv(name);
+    return (v && *v) ? std::string(v) : dflt;
+}
+
+bool parse_size(const std::string &s, size_t &out) {
+    if (s.empty()) return false;
+    char *end = nullptr;
+    errno = 0;
+    unsigned long long v = std::strtoull(s.c_str(), &end, 10);
+    if (errno || !end || *end) return false;
+    out = (size_t)v;
+    return true;
+}
+
+bool parse_ll(const std::string &s, long long &out) {
+    if (s.empty()) return false;
+    char *end = nullptr;
+    errno = 0;
+    long long v = std::strtoll(s.c_str(), &end, 10);
+    if (errno || !end || *end) return false;
+    out = v;
+    return true;
+}
+
+int env_int(const char *name, int dflt) {
+    long long v;
+    return parse_ll(env_or(name, ""), v) ? (int)v : dflt;
+}
+
+bool ends_with(const std::string &s, const std::string &suffix) {
+    return s.size() >= suffix.size() && s.compare(s.size() - suffix.size(), suffix.size(), suffix) == 0;
+}
+
+}  // namespace
+
+bool parse_bool(const std::string &s, bool dflt) {
+    if (s.empty()) return dflt;
+    if (s == "1" || s == "true" || s == "TRUE" || s == "True" || s == "t" || s == "T") return true;
+    if (s == "0" || s == "false" || s == "FALSE" || s == "False" || s == "f" || s == "F") return false;
+    return dflt;
+}
+
+bool parse_config(int argc, char **argv, Config &cfg) {
+    cfg.component = env_or("COMPONENT", "");
+    cfg.with_wait = parse_bool(env_or("WITH_WAIT", ""), false);
+    cfg.with_workload = parse_bool(env_or("WITH_WORKLOAD", ""), true);
+    cfg.output_dir = env_or("OUTPUT_DIR", "/run/nvidia/validations");
+    cfg.node_name = env_or("NODE_NAME", "");
+    cfg.operator_namespace = env_or("OPERATOR_NAMESPACE", "");
+    cfg.visible_devices = env_or("NVIDIA_VISIBLE_DEVICES", "");
+    cfg.mode = env_or("B200V_MODE", "validate");
+    size_t elems;
+    if (parse_size(env_or("B200V_ELEMS", ""), elems)) cfg.elems = elems;
+    cfg.gpus = env_int("B200V_GPUS", 0);
+    cfg.sleep_seconds = env_int("B200V_SLEEP_SECONDS", 5);
+    cfg.max_retries = env_int("B200V_MAX_RETRIES", 0);
+    long long inj;
+    if (parse_ll(env_or("B200V_INJECT_FAULT", ""), inj)) cfg.inject_fault = inj;
+    cfg.child_device = env_int("B200V_CHILD_DEVICE", -1);
+    cfg.nvidia_smi = env_or("B200V_NVIDIA_SMI", "nvidia-smi");
+    cfg.driver_root = env_or("DRIVER_ROOT", "/run/nvidia/driver");
+    char self[4096];
+    ssize_t len = readlink("/proc/self/exe", self, sizeof(self) - 1);
+    cfg.self_exe = len > 0 ? std::string(self, (size_t)len) : (argc > 0 ? argv[0] : "");
+
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i], val;
+        bool has_val = false;
+        size_t eq = a.find('=');
+        if (a.rfind("--", 0) == 0 && eq != std::string::npos) {
+            val = a.substr(eq + 1);
+            a = a.substr(0, eq);
+            has_val = true;
+        }
+        auto need = [&](std::string &dst) -> bool {
+            if (has_val) { dst = val; return true; }
+            if (i + 1 >= argc) { cfg.error = "flag needs an argument: " + a; return false; }
+            dst = argv[++i];
+            return true;
+        };
+        auto flag_bool = [&](bool &dst) {
+            // urfave/cli style: a bare bool flag means true; --flag=false is accepted
+            dst = has_val ? parse_bool(val, true) : true;
+        };
+        std::string tmp;
+        if (a == "--component" || a == "-c") { if (!need(cfg.component)) return false; }
+        else if (a == "--with-wait" || a == "-w") flag_bool(cfg.with_wait);
+        else if (a == "--with-workload" || a == "-l") flag_bool(cfg.with_workload);
+        else if (a == "--output-dir" || a == "-o") { if (!need(cfg.output_dir)) return false; }
+        else if (a == "--node-name") { if (!need(cfg.node_name)) return false; }
+        else if (a == "--namespace" || a == "-n") { if (!need(cfg.operator_namespace)) return false; }
+        else if (a == "--mode") { if (!need(cfg.mode)) return false; }
+        else if (a == "--elems") {
+            if (!need(tmp)) return false;
+            if (!parse_size(tmp, cfg.elems)) { cfg.error = "bad --elems: " + tmp; return false; }
+        } else if (a == "--gpus") {
+            if (!need(tmp)) return false;
+            long long g;
+            if (!parse_ll(tmp, g) || g < 0) { cfg.error = "bad --gpus: " + tmp; return false; }
+            cfg.gpus = (int)g;
+        } else {
+            cfg.error = "flag provided but not defined: " + a;
+            return false;
+        }
+    }
+    if (cfg.mode != "validate" && cfg.mode != "stream" && cfg.mode != "nccl") {
+        cfg.error = "B200V_MODE must be validate, stream or nccl, not " + cfg.mode;
+        return false;
+    }
+    return true;
+}
+
+// ---- status files ---------------------------------------------------------------------------------
+
+std::string status_path(const Config &cfg, const std::string &name) {
+    return cfg.output_dir + (ends_with(cfg.output_dir, "/") ? "" : "/") + name;
+}
+
+bool create_status_file(const Config &cfg, const std::string &name) {
+    const std::string p = status_path(cfg, name);
+    int fd = ::open(p.c_str(), O_CREAT | O_WRONLY | O_TRUNC, 0644);
+    if (fd < 0) return false;
+    ::close(fd);
+    return true;
+}
+
+bool delete_status_file(const Config &cfg, const std::string &name) {
+    const std::string p = status_path(cfg, name);
+    if (::unlink(p.c_str()) == 0) return true;
+    return errno == ENOENT;
+}
+
+namespace {
+// Removes cuda-gpu<i>-ready left by an earlier run (same effect as upstream's preStop rm -f).
+bool delete_per_gpu_files(const Config &cfg) {
+    DIR *d = ::opendir(cfg.output_dir.c_str());
+    if (!d) return errno == ENOENT;
+    bool ok = true;
+    while (dirent *e = ::readdir(d)) {
+        std::string name = e->d_name;
+        if (name.rfind("cuda-gpu", 0) == 0 && ends_with(name, "-ready")) ok = delete_status_file(cfg, name) && ok;
+    }
+    ::closedir(d);
+    return ok;
+}
+}  // namespace
+
+// ---- the sample -------------------------------------------------------------------------------------
+
+long long verify_result(const float *A, const float *B, const float *C, size_t n) {
+    for (size_t i = 0; i < n; ++i)
+        if (std::fabs(A[i] + B[i] - C[i]) > 1e-5) return (long long)i;
+    return -1;
+}
+
+int run_vectoradd_sample(const Api &api, int dev, size_t n, long long inject_fault, FILE *out, FILE *err) {
+    std::fprintf(out, "[Vector addition of %zu elements]\n", n);
+    float *A = (float *)std::malloc(n ? n * sizeof(float) : 1);
+    float *B = (float *)std::malloc(n ? n * sizeof(float) : 1);
+    float *C = (float *)std::malloc(n ? n * sizeof(float) : 1);
+    struct Free {
+        float *a, *b, *c;
+        ~Free() { std::free(a); std::free(b); std::free(c); }
+    } guard{A, B, C};
+    if (!A || !B || !C) {
+        std::fprintf(err, "Failed to allocate host vectors!\n");
+        return 1;
+    }
+    // Host init as in the sample: glibc rand() at its default seed, A and B drawn alternately.
+    std::srand(1);
+    for (size_t i = 0; i < n; ++i) {
+        A[i] = std::rand() / (float)RAND_MAX;
+        B[i] = std::rand() / (float)RAND_MAX;
+    }
+    std::fprintf(out, "Copy input data from the host memory to the CUDA device\n");
+    b200v_timing t;
+    std::memset(&t, 0, sizeof t);
+    int rc = api.vectoradd(dev, A, B, C, n, &t);
+    if (rc != B200V_OK) {
+        std::fprintf(err, "Failed to launch vectorAdd kernel (error code %s)!\n", api.strerror(rc));
+        return 1;
+    }
+    std::fprintf(out, "CUDA kernel launch with %d blocks of %d threads\n", t.grid, t.block);
+    std::fprintf(out, "Copy output data from the CUDA device to the host memory\n");
+    if (inject_fault >= 0 && (size_t)inject_fault < n) C[inject_fault] += 1.0f;
+
+    long long bad = verify_result(A, B, C, n);
+    if (bad >= 0) {
+        std::fprintf(err, "Result verification failed at element %lld!\n", bad);
+        return 1;
+    }
+    // Stricter than the sample: IEEE fp32 add is deterministic, so the bytes must match too.
+    for (size_t i = 0; i < n; ++i) {
+        const float want = A[i] + B[i] + 0.0f;
+        if (std::memcmp(&want, &C[i], sizeof(float)) != 0) {
+            std::fprintf(err, "Result verification failed at element %zu! (bitwise)\n", i);
+            return 1;
+        }
+    }
+    std::fprintf(out, "Test PASSED\n");
+    std::fprintf(out, "Done\n");
+    std::fflush(out);
+    return 0;
+}
+
+// ---- process helpers ---------------------------------------------------------------------------------
+
+int run_command(const std::string &cmd) {
+    int st = std::system(cmd.c_str());
+    if (st == -1) return -1;
+    if (WIFEXITED(st)) return WEXITSTATUS(st);
+    return 128 + (WIFSIGNALED(st) ? WTERMSIG(st) : 0);
+}
+
+std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::string> &argv) {
+    std::vector<pid_t> pids((size_t)ndev, -1);
+    std::vector<int> results((size_t)ndev, 1);
+    std::fflush(nullptr);
+    for (int i = 0; i < ndev; ++i) {
+        pid_t pid = ::fork();
+        if (pid == 0) {
+            ::setenv("B200V_CHILD_DEVICE", std::to_string(i).c_str(), 1);
+            std::vector<char *> av;
+            av.push_back(const_cast<char *>(cfg.self_exe.c_str()));
+            for (const std::string &a : argv) av.push_back(const_cast<char *>(a.c_str()));
+            av.push_back(nullptr);
+            ::execv(cfg.self_exe.c_str(), av.data());
+            ::_exit(127);
+        }
+        pids[(size_t)i] = pid;
+    }
+    for (int i = 0; i < ndev; ++i) {
+        if (pids[(size_t)i] < 0) continue;
+        int st = 0;
+        if (::waitpid(pids[(size_t)i], &st, 0) < 0) continue;
+        results[(size_t)i] = WIFEXITED(st) ? WEXITSTATUS(st) : 128 + (WIFSIGNALED(st) ? WTERMSIG(st) : 0);
+    }
+    return results;
+}
+
+// ---- COMPONENT handlers --------------------------------------------------------------------------------
+
+int validate_cuda(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    if (!delete_status_file(cfg, "cuda-ready") || !delete_per_gpu_files(cfg)) {
+        std::fprintf(err, "unable to remove stale status files under %s: %s\n", cfg.output_dir.c_str(),
+                     std::strerror(errno));
+        return 1;
+    }
+    int ndev = 0;
+    int rc = api.device_count(&ndev);
+    if (rc != B200V_OK || ndev < 1) {
+        std::fprintf(err, "cuda validation failed: %s\n", api.strerror(rc != B200V_OK ? rc : B200V_E_NODEVICE));
+        return 1;
+    }
+    if (cfg.gpus > ndev) {
+        std::fprintf(err, "cuda validation failed: B200V_GPUS=%d but only %d device(s) visible\n", cfg.gpus, ndev);
+        return 1;
+    }
+    const int use = cfg.gpus > 0 ? cfg.gpus : ndev;
+    std::vector<int> results;
+    if (use == 1) {
+        results.push_back(run_vectoradd_sample(api, 0, cfg.elems, cfg.inject_fault, out, err));
+    } else {
+        // One validator instance per device: independent shards, no exchange.
+        std::vector<std::string> args = {"--component", "cuda", "--output-dir", cfg.output_dir, "--elems",
+                                         std::to_string(cfg.elems)};
+        results = fan_out(cfg, use, args);
+    }
+    bool all = true;
+    for (int i = 0; i < use; ++i) {
+        if (results[(size_t)i] == 0) {
+            if (!create_status_file(cfg, "cuda-gpu" + std::to_string(i) + "-ready")) {
+                std::fprintf(err, "unable to create status file for gpu %d: %s\n", i, std::strerror(errno));
+                all = false;
+            }
+        } else {
+            std::fprintf(err, "cuda validation failed on gpu %d (exit code %d)\n", i, results[(size_t)i]);
+            all = false;
+        }
+    }
+    if (!all) return 1;
+    if (!create_status_file(cfg, "cuda-ready")) {
+        std::fprintf(err, "unable to create status file %s: %s\n", status_path(cfg, "cuda-ready").c_str(),
+                     std::strerror(errno));
+        return 1;
+    }
+    std::fprintf(out, "cuda workload validation is successful on %d device(s)\n", use);
+    return 0;
+}
+
+namespace {
+int validate_with_smi(const Config &cfg, const std::string &file, const std::string &cmd, const char *what,
+                      FILE *out, FILE *err) {
+    if (!delete_status_file(cfg, file)) {
+        std::fprintf(err, "unable to remove stale %s: %s\n", file.c_str(), std::strerror(errno));
+        return 1;
+    }
+    std::fflush(nullptr);
+    int rc = run_command(cmd);
+    if (rc != 0) {
+        std::fprintf(err, "%s validation failed: `%s` exited with %d\n", what, cmd.c_str(), rc);
+        return 1;
+    }
+    if (!create_status_file(cfg, file)) {
+        std::fprintf(err, "unable to create status file %s: %s\n", file.c_str(), std::strerror(errno));
+        return 1;
+    }
+    std::fprintf(out, "%s validation is successful\n", what);
+    return 0;
+}
+}  // namespace
+
+int validate_driver(const Config &cfg, FILE *out, FILE *err) {
+    // Containerised driver: nvidia-smi lives under the driver root (what the runbook execs into at
+    // reference README.md:152); host-installed driver: plain nvidia-smi.
+    struct stat st;
+    const std::string in_root = cfg.driver_root + "/usr/bin/nvidia-smi";
+    std::string cmd = cfg.nvidia_smi;
+    if (cfg.nvidia_smi == "nvidia-smi" && ::stat(in_root.c_str(), &st) == 0)
+        cmd = "chroot " + cfg.driver_root + " nvidia-smi";
+    return validate_with_smi(cfg, "driver-ready", cmd, "driver", out, err);
+}
+
+int validate_toolkit(const Config &cfg, FILE *out, FILE *err) {
+    return validate_with_smi(cfg, "toolkit-ready", cfg.nvidia_smi, "toolkit", out, err);
+}
+
+// ---- sweeps -------------------------------------------------------------------------------------------
+
+int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    int ndev = 0;
+    int rc = api.device_count(&ndev);
+    if (rc != B200V_OK || ndev < 1) {
+        std::fprintf(err, "stream sweep failed: %s\n", api.strerror(rc != B200V_OK ? rc : B200V_E_NODEVICE));
+        return 1;
+    }
+    const int dev = cfg.child_device >= 0 ? cfg.child_device : 0;
+    const int lo = env_int("B200V_MIN_LOG2", 18), hi = env_int("B200V_MAX_LOG2", 32);
+    const int ops[] = {B200V_OP_COPY, B200V_OP_SCALE, B200V_OP_ADD, B200V_OP_TRIAD};
+    b200v_info info;
+    std::memset(&info, 0, sizeof info);
+    api.device_info(dev, &info);
+    const double nominal = 2.0 * info.mem_clock_khz * 1e3 * info.mem_bus_bits / 8.0 / 1e9;
+    int failures = 0;
+    for (int lg = lo; lg <= hi; ++lg) {
+        const size_t n = (size_t)1 << lg;
+        for (int op : ops) {
+            b200v_stream_result r;
+            rc = api.stream(dev, op, n, 3.0f, 0xB200, 5, 20, &r);
+            if (rc != B200V_OK && rc != B200V_E_MISMATCH) {
+                std::fprintf(err, "stream %s n=2^%d failed: %s\n", kOpNames[op], lg, api.strerror(rc));
+                ++failures;
+                continue;
+            }
+            if (r.mismatches) ++failures;
+            std::fprintf(out,
+                         "{\"mode\":\"stream\",\"gpu\":%d,\"op\":\"%s\",\"log2_n\":%d,\"bytes_per_array\":%zu,"
+                         "\"best_ms\":%.5f,\"median_ms\":%.5f,\"best_gbs\":%.1f,\"median_gbs\":%.1f,"
+                         "\"l2_resident\":%d,\"frac_of_nominal\":%.4f,\"nominal_gbs\":%.0f,\"grid\":%d,\"block\":%d,"
+                         "\"mismatches\":%" PRIu64 ",\"digest\":\"%016" PRIx64 "\"}\n",
+                         dev, kOpNames[op], lg, n * 4, r.best_ms, r.median_ms, r.best_gbs, r.median_gbs,
+                         r.l2_resident, nominal > 0 ? r.median_gbs / nominal : 0.0, nominal, r.grid, r.block,
+                         r.mismatches, r.digest);
+            std::fflush(out);
+        }
+    }
+    return failures ? 1 : 0;
+}
+
+int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    int ndev = 0;
+    int rc = api.device_count(&ndev);
+    if (rc != B200V_OK || ndev < 1) {
+        std::fprintf(err, "nccl probe failed: %s\n", api.strerror(rc != B200V_OK ? rc : B200V_E_NODEVICE));
+        return 1;
+    }
+    const int use = cfg.gpus > 0 ? cfg.gpus : ndev;
+    if (use > ndev) {
+        std::fprintf(err, "nccl probe failed: B200V_GPUS=%d but only %d device(s) visible\n", use, ndev);
+        return 1;
+    }
+    std::vector<int> devs((size_t)use);
+    for (int i = 0; i < use; ++i) devs[(size_t)i] = i;
+    std::vector<b200v_ar_row> rows(64);
+    int nrows = 0;
+    const size_t lo = (size_t)1 << env_int("B200V_MIN_LOG2", 10), hi = (size_t)1 << env_int("B200V_MAX_LOG2", 30);
+    rc = api.allreduce_probe(use, devs.data(), lo, hi, 5, 20, rows.data(), (int)rows.size(), &nrows);
+    int failures = rc != B200V_OK ? 1 : 0;
+    if (rc != B200V_OK) std::fprintf(err, "nccl probe failed: %s\n", api.strerror(rc));
+    const double min_busbw = std::atof(env_or("B200V_MIN_BUSBW_GBS", "0").c_str());
+    for (int i = 0; i < nrows; ++i) {
+        const b200v_ar_row &r = rows[(size_t)i];
+        if (r.mismatches) ++failures;
+        std::fprintf(out,
+                     "{\"mode\":\"nccl\",\"ranks\":%d,\"bytes\":%" PRIu64 ",\"best_ms\":%.5f,\"median_ms\":%.5f,"
+                     "\"algbw_gbs\":%.2f,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%" PRIu64 "}\n",
+                     use, r.bytes, r.best_ms, r.median_ms, r.algbw_gbs, r.busbw_gbs, r.busbw_gbs / 900.0,
+                     r.mismatches);
+    }
+    if (nrows > 0 && min_busbw > 0 && rows[(size_t)nrows - 1].busbw_gbs < min_busbw) {
+        std::fprintf(err, "nccl probe failed: busBW %.1f GB/s below the required %.1f GB/s\n",
+                     rows[(size_t)nrows - 1].busbw_gbs, min_busbw);
+        ++failures;
+    }
+    std::fflush(out);
+    return failures ? 1 : 0;
+}
+
+// ---- executables -----------------------------------------------------------------------------------------
+
+int validator_main(const Api &api, int argc, char **argv) {
+    Config cfg;
+    if (!parse_config(argc, argv, cfg)) {
+        std::fprintf(stderr, "Incorrect Usage. %s\n", cfg.error.c_str());
+        return 1;
+    }
+    if (cfg.mode == "stream") return run_stream_sweep(api, cfg, stdout, stderr);
+    if (cfg.mode == "nccl") return run_nccl_probe(api, cfg, stdout, stderr);
+    if (cfg.component.empty()) {
+        std::fprintf(stderr, "invalid -c <component-name> flag: must not be empty string\n");
+        return 1;
+    }
+    if (cfg.child_device >= 0) {   // fan-out child: validate exactly one device, no status files
+        const long long inj = (env_int("B200V_INJECT_DEVICE", -1) < 0 ||
+                               env_int("B200V_INJECT_DEVICE", -1) == cfg.child_device) ? cfg.inject_fault : -1;
+        return run_vectoradd_sample(api, cfg.child_device, cfg.elems, inj, stdout, stderr);
+    }
+    auto once = [&]() -> int {
+        if (cfg.component == "cuda") return validate_cuda(api, cfg, stdout, stderr);
+        if (cfg.component == "driver") return validate_driver(cfg, stdout, stderr);
+        if (cfg.component == "toolkit") return validate_toolkit(cfg, stdout, stderr);
+        return -1;
+    };
+    int tries = 0;
+    for (;;) {
+        int rc = once();
+        if (rc == -1) {
+            // plugin, mofed, vfio-pci, vgpu-manager, vgpu-devices, cc-manager, nvidia-fs and metrics
+            // belong to other parts of the operator; this image covers the GPU workload path only.
+            std::fprintf(stderr, "invalid component specified for validation: %s (this build supports cuda, "
+                                 "driver, toolkit)\n", cfg.component.c_str());
+            return 1;
+        }
+        if (rc == 0) return 0;
+        ++tries;
+        if (!cfg.with_wait || (cfg.max_retries > 0 && tries >= cfg.max_retries)) return 1;
+        std::fprintf(stderr, "%s is not ready, retrying after %d seconds\n", cfg.component.c_str(), cfg.sleep_seconds);
+        std::fflush(nullptr);
+        ::sleep((unsigned)cfg.sleep_seconds);
+    }
+}
+
+int vectoradd_main(const Api &api, int argc, char **argv) {
+    // The sample takes no arguments; B200V_ELEMS / --elems and B200V_GPUS are the only additions.
+    Config cfg;
+    if (!parse_config(argc, argv, cfg)) {
+        std::fprintf(stderr, "Incorrect Usage. %s\n", cfg.error.c_str());
+        return 1;
+    }
+    const int dev = cfg.child_device >= 0 ? cfg.child_device : 0;
+    int rc = run_vectoradd_sample(api, dev, cfg.elems, cfg.inject_fault, stdout, stderr);
+    api.shutdown();
+    return rc == 0 ? 0 : 1;
+}
+
+}  // namespace b200v_host

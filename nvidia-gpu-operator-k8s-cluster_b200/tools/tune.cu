@@ -159,6 +159,7 @@ int main(int argc, char **argv) {
     int last_ref_op = -1;
     const int grid_mults[] = {0, 1, 2, 3, 4, 6, 8, 12, 16, 32};
     for (const Cfg &c : g_cfgs) {
+        if (c.smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         if (c.smem) CK(cudaFuncSetAttribute((const void *)c.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem));
         int occ = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)c.fn, c.block, c.smem));

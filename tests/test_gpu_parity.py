@@ -217,8 +217,8 @@ print("VARIANT_OK" if ok else "VARIANT_BAD")
 """
 
 
-@pytest.mark.parametrize("variant", ["v8u2b256", "v4u4b256", "v4u4b256-oneshot", "v8u2b256-oneshot",
-                                     "bulk4096s4b256"])
+@pytest.mark.parametrize("variant", ["v8u1b256-oneshot", "v4u2b256-oneshot", "v8u2b1024-oneshot",
+                                     "v8u2b256-persist8", "v4u4b256-persist8", "bulk2048s3b128"])
 def test_kernel_variants(gpu, variant):
     env = dict(os.environ, B200V_EW_VARIANT=variant)
     out = subprocess.run([sys.executable, "-c", VARIANT_SCRIPT % {"root": ROOT}], env=env,

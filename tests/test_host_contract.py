@@ -1,0 +1,183 @@
+"""CPU tests of the validator contract: exit codes, <OUTPUT_DIR>/*-ready status
+files, the sample's output lines, per-GPU fan-out, WITH_WAIT retries, flag/env parsing.
+
+The product host logic (host/validator_core.cpp) is linked against tests/host/fake_main.cpp, a
+scripted stand-in for the C ABI, so the kubelet-facing behaviour is checked without a GPU.  The
+shell harness here plays kubelet: it runs the entrypoint with the DaemonSet's environment and
+looks at files and exit codes."""
+import json
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "nvidia-gpu-operator-k8s-cluster_b200")
+BUILD = os.path.join(ROOT, "tests", "host", "build")
+FAKE = os.path.join(BUILD, "fake-validator")
+
+
+@pytest.fixture(scope="session")
+def fake():
+    os.makedirs(BUILD, exist_ok=True)
+    srcs = [os.path.join(ROOT, "tests", "host", "fake_main.cpp"), os.path.join(PKG, "host", "validator_core.cpp")]
+    newest = max(os.path.getmtime(p) for p in srcs + [os.path.join(PKG, "host", "validator_core.h")])
+    if not os.path.exists(FAKE) or os.path.getmtime(FAKE) < newest:
+        subprocess.check_call(["g++", "-O1", "-std=c++17", "-Wall", "-I", os.path.join(ROOT, "include"),
+                               "-I", os.path.join(PKG, "host"), "-o", FAKE] + srcs)
+    return FAKE
+
+
+def run(fake, tmp_path, args=(), **env):
+    e = {"PATH": os.environ["PATH"], "OUTPUT_DIR": str(tmp_path), "B200V_SLEEP_SECONDS": "0"}
+    e.update({k: str(v) for k, v in env.items()})
+    p = subprocess.run([fake] + list(args), env=e, capture_output=True, text=True, timeout=60)
+    return p.returncode, p.stdout, p.stderr
+
+
+def ready(tmp_path):
+    return sorted(f for f in os.listdir(tmp_path) if f.endswith("-ready"))
+
+
+def test_cuda_single_gpu_pass(fake, tmp_path):
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda")
+    assert rc == 0, err
+    assert ready(tmp_path) == ["cuda-gpu0-ready", "cuda-ready"]
+    assert os.path.getsize(tmp_path / "cuda-ready") == 0
+    lines = out.splitlines()
+    assert lines[0] == "[Vector addition of 50000 elements]"
+    assert lines[1] == "Copy input data from the host memory to the CUDA device"
+    assert lines[2] == "CUDA kernel launch with 25 blocks of 256 threads"
+    assert lines[3] == "Copy output data from the CUDA device to the host memory"
+    assert lines[4] == "Test PASSED" and lines[5] == "Done"
+
+
+def test_cuda_failure_removes_stale_status_and_exits_1(fake, tmp_path):
+    (tmp_path / "cuda-ready").write_text("")
+    (tmp_path / "cuda-gpu0-ready").write_text("")
+    (tmp_path / "driver-ready").write_text("")          # another component's file is not ours to touch
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_MODE="wrong")
+    assert rc == 1
+    assert "Result verification failed at element 17!" in err
+    assert "Test PASSED" not in out
+    assert ready(tmp_path) == ["driver-ready"]
+
+
+def test_cuda_error_from_library_is_reported(fake, tmp_path):
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_MODE="cudaerr")
+    assert rc == 1 and "illegal memory access" in err
+    assert ready(tmp_path) == []
+
+
+def test_no_device_fails_without_status_file(fake, tmp_path):
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=0)
+    assert rc == 1 and "no CUDA device" in err
+    assert ready(tmp_path) == []
+
+
+def test_fault_injection_hits_the_verification_loop(fake, tmp_path):
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", B200V_INJECT_FAULT=4242)
+    assert rc == 1 and "Result verification failed at element 4242!" in err
+    assert ready(tmp_path) == []
+
+
+def test_fanout_all_pass(fake, tmp_path):
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=4)
+    assert rc == 0, err
+    assert ready(tmp_path) == ["cuda-gpu0-ready", "cuda-gpu1-ready", "cuda-gpu2-ready", "cuda-gpu3-ready",
+                               "cuda-ready"]
+    assert out.count("Test PASSED") == 4
+    assert "successful on 4 device(s)" in out
+
+
+def test_fanout_one_gpu_fails(fake, tmp_path):
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=4, FAKE_MODE="wrong", FAKE_FAIL_DEVICE=2)
+    assert rc == 1
+    assert ready(tmp_path) == ["cuda-gpu0-ready", "cuda-gpu1-ready", "cuda-gpu3-ready"]
+    assert "cuda validation failed on gpu 2 (exit code 1)" in err
+    assert out.count("Test PASSED") == 3
+
+
+def test_fanout_subset_and_oversubscription(fake, tmp_path):
+    rc, _out, _err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=8, B200V_GPUS=2)
+    assert rc == 0 and ready(tmp_path) == ["cuda-gpu0-ready", "cuda-gpu1-ready", "cuda-ready"]
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=2, B200V_GPUS=4)
+    assert rc == 1 and "only 2 device(s) visible" in err
+    assert ready(tmp_path) == []
+
+
+def test_with_wait_retries_until_limit(fake, tmp_path):
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", WITH_WAIT="true", FAKE_MODE="cudaerr",
+                        B200V_MAX_RETRIES=3)
+    assert rc == 1
+    assert err.count("cuda is not ready, retrying after 0 seconds") == 2
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", WITH_WAIT="false", FAKE_MODE="cudaerr")
+    assert rc == 1 and "retrying" not in err
+
+
+def test_flags_override_environment(fake, tmp_path):
+    other = tmp_path / "elsewhere"
+    other.mkdir()
+    rc, out, _err = run(fake, tmp_path, args=["--component", "cuda", "--output-dir=%s" % other, "--elems", "4096"],
+                        COMPONENT="bogus")
+    assert rc == 0 and "[Vector addition of 4096 elements]" in out
+    assert ready(other) == ["cuda-gpu0-ready", "cuda-ready"] and ready(tmp_path) == []
+    rc, _out, err = run(fake, tmp_path, args=["--no-such-flag"], COMPONENT="cuda")
+    assert rc == 1 and "flag provided but not defined: --no-such-flag" in err
+    rc, _out, err = run(fake, tmp_path, args=["-c"], COMPONENT="cuda")
+    assert rc == 1 and "flag needs an argument" in err
+
+
+def test_component_validation(fake, tmp_path):
+    rc, _out, err = run(fake, tmp_path)
+    assert rc == 1 and "must not be empty string" in err
+    for comp in ("plugin", "mofed", "metrics", "nope"):
+        rc, _out, err = run(fake, tmp_path, COMPONENT=comp)
+        assert rc == 1 and "invalid component specified for validation: %s" % comp in err
+    assert ready(tmp_path) == []
+
+
+def test_driver_and_toolkit_use_nvidia_smi(fake, tmp_path):
+    rc, out, _err = run(fake, tmp_path, COMPONENT="toolkit", B200V_NVIDIA_SMI="true")
+    assert rc == 0 and ready(tmp_path) == ["toolkit-ready"] and "toolkit validation is successful" in out
+    rc, out, _err = run(fake, tmp_path, COMPONENT="driver", B200V_NVIDIA_SMI="true")
+    assert rc == 0 and ready(tmp_path) == ["driver-ready", "toolkit-ready"]
+    rc, _out, err = run(fake, tmp_path, COMPONENT="driver", B200V_NVIDIA_SMI="false")
+    assert rc == 1 and "driver validation failed" in err
+    assert ready(tmp_path) == ["toolkit-ready"]          # stale driver-ready removed, toolkit's kept
+
+
+def test_unwritable_output_dir_fails(fake, tmp_path):
+    rc, _out, err = run(fake, tmp_path, COMPONENT="cuda", OUTPUT_DIR=str(tmp_path / "missing" / "dir"))
+    assert rc == 1 and "unable to create status file" in err
+
+
+def test_vectoradd_entrypoint(fake, tmp_path):
+    rc, out, _err = run(fake, tmp_path, FAKE_ENTRY="vectoradd")
+    assert rc == 0 and out.splitlines()[-2:] == ["Test PASSED", "Done"]
+    assert ready(tmp_path) == []                          # the sample binary writes no status file
+    rc, out, err = run(fake, tmp_path, FAKE_ENTRY="vectoradd", FAKE_MODE="wrong")
+    assert rc == 1 and "Result verification failed at element 17!" in err
+    rc, out, _err = run(fake, tmp_path, FAKE_ENTRY="vectoradd", B200V_ELEMS=0)
+    assert rc == 0 and "[Vector addition of 0 elements]" in out
+
+
+def test_stream_and_nccl_modes_emit_json_rows(fake, tmp_path):
+    rc, out, _err = run(fake, tmp_path, B200V_MODE="stream", B200V_MIN_LOG2=18, B200V_MAX_LOG2=19)
+    assert rc == 0
+    rows = [json.loads(line) for line in out.splitlines()]
+    assert [(r["op"], r["log2_n"]) for r in rows] == [(op, lg) for lg in (18, 19)
+                                                      for op in ("copy", "scale", "add", "triad")]
+    assert rows[0]["bytes_per_array"] == 1 << 20 and rows[0]["nominal_gbs"] == 8184
+    rc, _out, _err = run(fake, tmp_path, B200V_MODE="stream", B200V_MAX_LOG2=18, FAKE_MODE="wrong")
+    assert rc == 1
+    rc, out, _err = run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=8, B200V_MIN_LOG2=10, B200V_MAX_LOG2=12)
+    assert rc == 0
+    rows = [json.loads(line) for line in out.splitlines()]
+    assert [r["bytes"] for r in rows] == [1024, 2048, 4096] and rows[0]["ranks"] == 8
+    assert abs(rows[0]["busbw_gbs"] - 400 * 2 * 7 / 8) < 1e-6
+    rc, _out, err = run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=8, B200V_MIN_BUSBW_GBS=720,
+                        B200V_MAX_LOG2=12)
+    assert rc == 1 and "below the required 720.0 GB/s" in err
+    rc, _out, _err = run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=2, FAKE_MODE="wrong", B200V_MAX_LOG2=12)
+    assert rc == 1
