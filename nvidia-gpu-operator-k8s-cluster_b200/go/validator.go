@@ -1,0 +1,402 @@
+// Package main — cgo driver of the B200 node validator.
+//
+// NOT COMPILED IN THIS ENVIRONMENT: the build image and the GPU box have no Go toolchain
+// (`go: command not found`).  This file mirrors host/validator_core.cpp function for function over
+// the same C ABI (include/b200validate.h); the C++ twin is what the tests build and run.  Keep the
+// two in step: a behaviour change goes into both.
+//
+// Contract (operator-validator, SURVEY.md §8b): COMPONENT / WITH_WAIT / WITH_WORKLOAD /
+// OUTPUT_DIR environment (each mirrored by a flag), exit code 0 or 1, empty status files
+// <OUTPUT_DIR>/{cuda,driver,toolkit}-ready created on success and removed before validating.
+//
+// Build (on a machine that has Go):
+//   CGO_CFLAGS="-I${REPO}/include" CGO_LDFLAGS="-L${REPO}/nvidia-gpu-operator-k8s-cluster_b200/lib -lb200validate" \
+//   go build -o nvidia-validator ./go
+package main
+
+/*
+#include <stdlib.h>
+#include "b200validate.h"
+*/
+import "C"
+
+import (
+	"flag"
+	"fmt"
+	"math"
+	"os"
+	"os/exec"
+	"path/filepath"
+	"runtime"
+	"strconv"
+	"strings"
+	"sync"
+	"time"
+	"unsafe"
+)
+
+type config struct {
+	component, outputDir, nodeName, namespace, mode, nvidiaSmi, driverRoot string
+	withWait, withWorkload                                                bool
+	elems                                                                 uint64
+	gpus, sleepSeconds, maxRetries, childDevice                           int
+	injectFault                                                           int64
+}
+
+func envOr(name, dflt string) string {
+	if v := os.Getenv(name); v != "" {
+		return v
+	}
+	return dflt
+}
+
+func envInt(name string, dflt int) int {
+	if v, err := strconv.Atoi(os.Getenv(name)); err == nil {
+		return v
+	}
+	return dflt
+}
+
+func envBool(name string, dflt bool) bool {
+	if v, err := strconv.ParseBool(os.Getenv(name)); err == nil {
+		return v
+	}
+	return dflt
+}
+
+// parseConfig: environment first, flags win (same order as parse_config in the C++ twin).
+func parseConfig() (*config, error) {
+	c := &config{}
+	fs := flag.NewFlagSet("nvidia-validator", flag.ContinueOnError)
+	fs.StringVar(&c.component, "component", envOr("COMPONENT", ""), "component to validate: cuda, driver, toolkit")
+	fs.BoolVar(&c.withWait, "with-wait", envBool("WITH_WAIT", false), "retry until the validation succeeds")
+	fs.BoolVar(&c.withWorkload, "with-workload", envBool("WITH_WORKLOAD", true), "run the CUDA workload")
+	fs.StringVar(&c.outputDir, "output-dir", envOr("OUTPUT_DIR", "/run/nvidia/validations"), "status file directory")
+	fs.StringVar(&c.nodeName, "node-name", envOr("NODE_NAME", ""), "node name")
+	fs.StringVar(&c.namespace, "namespace", envOr("OPERATOR_NAMESPACE", ""), "operator namespace")
+	fs.StringVar(&c.mode, "mode", envOr("B200V_MODE", "validate"), "validate | stream | nccl")
+	fs.Uint64Var(&c.elems, "elems", uint64(envInt("B200V_ELEMS", 50000)), "elements per vector")
+	fs.IntVar(&c.gpus, "gpus", envInt("B200V_GPUS", 0), "devices to validate (0 = all visible)")
+	if err := fs.Parse(os.Args[1:]); err != nil {
+		return nil, err
+	}
+	c.sleepSeconds = envInt("B200V_SLEEP_SECONDS", 5)
+	c.maxRetries = envInt("B200V_MAX_RETRIES", 0)
+	c.childDevice = envInt("B200V_CHILD_DEVICE", -1)
+	c.injectFault = int64(envInt("B200V_INJECT_FAULT", -1))
+	c.nvidiaSmi = envOr("B200V_NVIDIA_SMI", "nvidia-smi")
+	c.driverRoot = envOr("DRIVER_ROOT", "/run/nvidia/driver")
+	if c.mode != "validate" && c.mode != "stream" && c.mode != "nccl" {
+		return nil, fmt.Errorf("B200V_MODE must be validate, stream or nccl, not %s", c.mode)
+	}
+	return c, nil
+}
+
+func strerror(code C.int) string { return C.GoString(C.b200v_strerror(code)) }
+
+func statusPath(c *config, name string) string { return filepath.Join(c.outputDir, name) }
+
+func createStatusFile(c *config, name string) error {
+	f, err := os.Create(statusPath(c, name))
+	if err != nil {
+		return err
+	}
+	return f.Close()
+}
+
+func deleteStatusFile(c *config, name string) error {
+	err := os.Remove(statusPath(c, name))
+	if err != nil && !os.IsNotExist(err) {
+		return err
+	}
+	return nil
+}
+
+// glibcRand reproduces the sample's unseeded rand() stream (TYPE_3, seed 1) so the Go driver fills
+// the same inputs the C sample does without calling into libc from Go.
+type glibcRand struct {
+	r []uint32
+	k int
+}
+
+func newGlibcRand(seed int32) *glibcRand {
+	g := &glibcRand{r: make([]uint32, 34, 4096)}
+	g.r[0] = uint32(seed)
+	for i := 1; i < 31; i++ {
+		hi, lo := int64(int32(g.r[i-1]))/127773, int64(int32(g.r[i-1]))%127773
+		w := 16807*lo - 2836*hi
+		if w < 0 {
+			w += 2147483647
+		}
+		g.r[i] = uint32(w)
+	}
+	for i := 31; i < 34; i++ {
+		g.r[i] = g.r[i-31]
+	}
+	for i := 34; i < 344; i++ {
+		g.r = append(g.r, g.r[i-31]+g.r[i-3])
+	}
+	g.k = 344
+	return g
+}
+
+func (g *glibcRand) next() int32 {
+	v := g.r[g.k-31] + g.r[g.k-3]
+	g.r = append(g.r, v)
+	g.k++
+	return int32(v >> 1)
+}
+
+// runVectorAddSample mirrors run_vectoradd_sample: host init, device add through the C ABI, the
+// sample's verification loop, then a bitwise check.
+func runVectorAddSample(dev int, n uint64, injectFault int64) int {
+	runtime.LockOSThread() // CUDA's current device is per OS thread
+	defer runtime.UnlockOSThread()
+	fmt.Printf("[Vector addition of %d elements]\n", n)
+	a, b, out := make([]float32, n+1), make([]float32, n+1), make([]float32, n+1)
+	rng := newGlibcRand(1)
+	const randMax = float32(2147483647)
+	for i := uint64(0); i < n; i++ {
+		a[i] = float32(rng.next()) / randMax
+		b[i] = float32(rng.next()) / randMax
+	}
+	fmt.Println("Copy input data from the host memory to the CUDA device")
+	var t C.b200v_timing
+	rc := C.b200v_vectoradd(C.int(dev), (*C.float)(unsafe.Pointer(&a[0])), (*C.float)(unsafe.Pointer(&b[0])),
+		(*C.float)(unsafe.Pointer(&out[0])), C.size_t(n), &t)
+	if rc != 0 {
+		fmt.Fprintf(os.Stderr, "Failed to launch vectorAdd kernel (error code %s)!\n", strerror(rc))
+		return 1
+	}
+	fmt.Printf("CUDA kernel launch with %d blocks of %d threads\n", int(t.grid), int(t.block))
+	fmt.Println("Copy output data from the CUDA device to the host memory")
+	if injectFault >= 0 && uint64(injectFault) < n {
+		out[injectFault] += 1.0
+	}
+	for i := uint64(0); i < n; i++ {
+		if math.Abs(float64(a[i]+b[i]-out[i])) > 1e-5 {
+			fmt.Fprintf(os.Stderr, "Result verification failed at element %d!\n", i)
+			return 1
+		}
+	}
+	for i := uint64(0); i < n; i++ {
+		want := a[i] + b[i] + 0.0
+		if math.Float32bits(want) != math.Float32bits(out[i]) {
+			fmt.Fprintf(os.Stderr, "Result verification failed at element %d! (bitwise)\n", i)
+			return 1
+		}
+	}
+	fmt.Println("Test PASSED")
+	fmt.Println("Done")
+	return 0
+}
+
+// validateCuda mirrors validate_cuda: one validator instance per device, status files per device,
+// cuda-ready only when every device passed.
+func validateCuda(c *config) int {
+	if err := deleteStatusFile(c, "cuda-ready"); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to remove stale status files under %s: %v\n", c.outputDir, err)
+		return 1
+	}
+	old, _ := filepath.Glob(statusPath(c, "cuda-gpu*-ready"))
+	for _, f := range old {
+		os.Remove(f)
+	}
+	var ndev C.int
+	if rc := C.b200v_device_count(&ndev); rc != 0 || ndev < 1 {
+		fmt.Fprintf(os.Stderr, "cuda validation failed: %s\n", strerror(rc))
+		return 1
+	}
+	if c.gpus > int(ndev) {
+		fmt.Fprintf(os.Stderr, "cuda validation failed: B200V_GPUS=%d but only %d device(s) visible\n", c.gpus, int(ndev))
+		return 1
+	}
+	use := int(ndev)
+	if c.gpus > 0 {
+		use = c.gpus
+	}
+	results := make([]int, use)
+	if use == 1 {
+		results[0] = runVectorAddSample(0, c.elems, c.injectFault)
+	} else {
+		self, _ := os.Executable()
+		var wg sync.WaitGroup
+		for i := 0; i < use; i++ {
+			wg.Add(1)
+			go func(i int) { // one child process per device: exit-code isolation
+				defer wg.Done()
+				cmd := exec.Command(self, "--component", "cuda", "--output-dir", c.outputDir, "--elems",
+					strconv.FormatUint(c.elems, 10))
+				cmd.Env = append(os.Environ(), "B200V_CHILD_DEVICE="+strconv.Itoa(i))
+				cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
+				if err := cmd.Run(); err != nil {
+					results[i] = 1
+				}
+			}(i)
+		}
+		wg.Wait()
+	}
+	all := true
+	for i, rc := range results {
+		if rc == 0 {
+			if err := createStatusFile(c, fmt.Sprintf("cuda-gpu%d-ready", i)); err != nil {
+				fmt.Fprintf(os.Stderr, "unable to create status file for gpu %d: %v\n", i, err)
+				all = false
+			}
+		} else {
+			fmt.Fprintf(os.Stderr, "cuda validation failed on gpu %d (exit code %d)\n", i, rc)
+			all = false
+		}
+	}
+	if !all {
+		return 1
+	}
+	if err := createStatusFile(c, "cuda-ready"); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to create status file %s: %v\n", statusPath(c, "cuda-ready"), err)
+		return 1
+	}
+	fmt.Printf("cuda workload validation is successful on %d device(s)\n", use)
+	return 0
+}
+
+func validateWithSmi(c *config, file, what string, argv []string) int {
+	if err := deleteStatusFile(c, file); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to remove stale %s: %v\n", file, err)
+		return 1
+	}
+	cmd := exec.Command(argv[0], argv[1:]...)
+	cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
+	if err := cmd.Run(); err != nil {
+		fmt.Fprintf(os.Stderr, "%s validation failed: `%s`: %v\n", what, strings.Join(argv, " "), err)
+		return 1
+	}
+	if err := createStatusFile(c, file); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to create status file %s: %v\n", file, err)
+		return 1
+	}
+	fmt.Printf("%s validation is successful\n", what)
+	return 0
+}
+
+func validateDriver(c *config) int {
+	argv := []string{c.nvidiaSmi}
+	if _, err := os.Stat(filepath.Join(c.driverRoot, "usr/bin/nvidia-smi")); err == nil && c.nvidiaSmi == "nvidia-smi" {
+		argv = []string{"chroot", c.driverRoot, "nvidia-smi"}
+	}
+	return validateWithSmi(c, "driver-ready", "driver", argv)
+}
+
+func validateToolkit(c *config) int {
+	return validateWithSmi(c, "toolkit-ready", "toolkit", []string{c.nvidiaSmi})
+}
+
+func runStreamSweep(c *config) int {
+	ops := []struct {
+		id   C.int
+		name string
+	}{{C.B200V_OP_COPY, "copy"}, {C.B200V_OP_SCALE, "scale"}, {C.B200V_OP_ADD, "add"}, {C.B200V_OP_TRIAD, "triad"}}
+	failures := 0
+	for lg := envInt("B200V_MIN_LOG2", 18); lg <= envInt("B200V_MAX_LOG2", 32); lg++ {
+		for _, op := range ops {
+			var r C.b200v_stream_result
+			rc := C.b200v_stream(0, op.id, C.size_t(1)<<uint(lg), 3.0, 0xB200, 5, 20, &r)
+			if rc != 0 && rc != C.B200V_E_MISMATCH {
+				fmt.Fprintf(os.Stderr, "stream %s n=2^%d failed: %s\n", op.name, lg, strerror(rc))
+				failures++
+				continue
+			}
+			if r.mismatches != 0 {
+				failures++
+			}
+			fmt.Printf("{\"mode\":\"stream\",\"op\":\"%s\",\"log2_n\":%d,\"median_gbs\":%.1f,\"best_gbs\":%.1f,"+
+				"\"l2_resident\":%d,\"mismatches\":%d,\"digest\":\"%016x\"}\n", op.name, lg, float64(r.median_gbs),
+				float64(r.best_gbs), int(r.l2_resident), uint64(r.mismatches), uint64(r.digest))
+		}
+	}
+	if failures > 0 {
+		return 1
+	}
+	return 0
+}
+
+func runNcclProbe(c *config) int {
+	var ndev C.int
+	if rc := C.b200v_device_count(&ndev); rc != 0 || ndev < 1 {
+		fmt.Fprintf(os.Stderr, "nccl probe failed: %s\n", strerror(rc))
+		return 1
+	}
+	use := int(ndev)
+	if c.gpus > 0 {
+		use = c.gpus
+	}
+	devs := make([]C.int, use)
+	for i := range devs {
+		devs[i] = C.int(i)
+	}
+	rows := make([]C.b200v_ar_row, 64)
+	var nrows C.int
+	rc := C.b200v_allreduce_probe(C.int(use), &devs[0], C.size_t(1)<<uint(envInt("B200V_MIN_LOG2", 10)),
+		C.size_t(1)<<uint(envInt("B200V_MAX_LOG2", 30)), 5, 20, &rows[0], 64, &nrows)
+	failures := 0
+	if rc != 0 {
+		fmt.Fprintf(os.Stderr, "nccl probe failed: %s\n", strerror(rc))
+		failures++
+	}
+	for i := 0; i < int(nrows); i++ {
+		r := rows[i]
+		if r.mismatches != 0 {
+			failures++
+		}
+		fmt.Printf("{\"mode\":\"nccl\",\"ranks\":%d,\"bytes\":%d,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%d}\n",
+			use, uint64(r.bytes), float64(r.busbw_gbs), float64(r.busbw_gbs)/900.0, uint64(r.mismatches))
+	}
+	if failures > 0 {
+		return 1
+	}
+	return 0
+}
+
+func main() {
+	c, err := parseConfig()
+	if err != nil {
+		fmt.Fprintf(os.Stderr, "Incorrect Usage. %v\n", err)
+		os.Exit(1)
+	}
+	switch c.mode {
+	case "stream":
+		os.Exit(runStreamSweep(c))
+	case "nccl":
+		os.Exit(runNcclProbe(c))
+	}
+	if c.component == "" {
+		fmt.Fprintln(os.Stderr, "invalid -c <component-name> flag: must not be empty string")
+		os.Exit(1)
+	}
+	if c.childDevice >= 0 {
+		os.Exit(runVectorAddSample(c.childDevice, c.elems, c.injectFault))
+	}
+	for tries := 0; ; {
+		rc := -1
+		switch c.component {
+		case "cuda":
+			rc = validateCuda(c)
+		case "driver":
+			rc = validateDriver(c)
+		case "toolkit":
+			rc = validateToolkit(c)
+		}
+		if rc == -1 {
+			fmt.Fprintf(os.Stderr, "invalid component specified for validation: %s (this build supports cuda, driver, toolkit)\n", c.component)
+			os.Exit(1)
+		}
+		if rc == 0 {
+			os.Exit(0)
+		}
+		tries++
+		if !c.withWait || (c.maxRetries > 0 && tries >= c.maxRetries) {
+			os.Exit(1)
+		}
+		fmt.Fprintf(os.Stderr, "%s is not ready, retrying after %d seconds\n", c.component, c.sleepSeconds)
+		time.Sleep(time.Duration(c.sleepSeconds) * time.Second)
+	}
+}
