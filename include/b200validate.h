@@ -41,6 +41,7 @@ extern "C" {
 #define B200V_E_NODEVICE   (-4)  /* no CUDA device visible */
 #define B200V_E_NONCCL     (-5)  /* libnccl.so.2 could not be loaded */
 #define B200V_E_NOMEM      (-6)  /* host allocation failed */
+#define B200V_E_TOOLARGE   (-7)  /* n exceeds the fixed capacity of a no-allocation entry point */
 
 /* Elementwise ops.  dst = f(x, y, s), fp32, round-to-nearest-even, denormals kept (no -ftz):
  *   COPY dst=x   SCALE dst=s*x   ADD dst=x+y   TRIAD dst=fmaf(s,y,x) (one FFMA)
@@ -123,6 +124,26 @@ int b200v_host_free(void *ptr);
  * three streams.  n == 0 is OK and a no-op.  timing may be NULL. */
 int b200v_vectoradd(int dev, const float *hA, const float *hB, float *hC, size_t n,
                     b200v_timing *timing);
+
+/* Has no counterpart in the reference or in the sample it deploys.  The same computation as
+ * b200v_vectoradd (hC[i] = hA[i] + hB[i] + 0.0f on host buffers) for callers that cannot
+ * allocate device memory: a validator re-run as a health probe on a GPU that is already serving a
+ * tenant, where HBM may be fully committed (cudaMalloc would fail and a healthy GPU would be
+ * reported broken) and where cudaMalloc/cudaFree would stall the tenant by synchronising the
+ * device.  It calls no allocator, creates no stream or event, and stages through a fixed array
+ * inside the library: 3 x B200V_NOALLOC_MAX_ELEMS floats (12 MiB) that every GPU which loads the
+ * library holds until the process exits.
+ *   - n > B200V_NOALLOC_MAX_ELEMS returns B200V_E_TOOLARGE and computes nothing.
+ *   - `stream` is the caller's cudaStream_t (NULL = default stream); the call enqueues two H2D
+ *     copies, the kernel and one D2H copy on it and returns after synchronising it.
+ *   - The first call on each GPU also performs that GPU's one-time set-up (looking up the
+ *     array's device address); make it before starting any stream capture.
+ *   - All calls on one GPU share the array, which still holds the previous call's data: calls
+ *     that overlap in time on the same GPU race with each other, so serialise them.  No clearing
+ *     is needed between calls (every element read was written earlier in the same call). */
+#define B200V_NOALLOC_MAX_ELEMS (1u << 20)
+int b200v_vectoradd_noalloc(int dev, const float *hA, const float *hB, float *hC, size_t n,
+                            void *stream);
 
 /* Same contract for any B200V_OP_* on host buffers: hDst = op(hX, hY, s).  hY is ignored (may be
  * NULL) for COPY and SCALE.  New (STREAM sweep). */

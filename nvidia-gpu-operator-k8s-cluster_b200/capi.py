@@ -69,6 +69,7 @@ SIGNATURES = {
     "b200v_host_alloc": (_i, [_P(_vp), _sz]),
     "b200v_host_free": (_i, [_vp]),
     "b200v_vectoradd": (_i, [_i, _vp, _vp, _vp, _sz, _P(Timing)]),
+    "b200v_vectoradd_noalloc": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "b200v_stream_host": (_i, [_i, _i, _vp, _vp, _vp, _f, _sz, _P(Timing)]),
     "b200v_vectoradd_device": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "b200v_stream_device": (_i, [_i, _i, _vp, _vp, _vp, _f, _sz, _vp]),
@@ -189,6 +190,18 @@ def vectoradd(hA, hB, hC, n=None, dev=0):
     t = Timing()
     _check(lib().b200v_vectoradd(dev, _ptr(hA), _ptr(hB), _ptr(hC), n, ctypes.byref(t)), "b200v_vectoradd")
     return t
+
+
+NOALLOC_MAX_ELEMS = 1 << 20
+E_TOOLARGE = -7
+
+
+def vectoradd_noalloc(hA, hB, hC, n=None, dev=0, stream=None):
+    """hC = hA + hB + 0.0f through b200v_vectoradd_noalloc: no device allocation, n capped at
+    NOALLOC_MAX_ELEMS (B200VError with code E_TOOLARGE beyond it)."""
+    n = hA.size if n is None else n
+    _check(lib().b200v_vectoradd_noalloc(dev, _ptr(hA), _ptr(hB), _ptr(hC), n, stream),
+           "b200v_vectoradd_noalloc")
 
 
 def stream_host(op, hDst, hX, hY=None, s=0.0, n=None, dev=0):

@@ -301,6 +301,7 @@ const char *b200v_strerror(int code) {
     case B200V_E_NODEVICE: return "no CUDA device";
     case B200V_E_NONCCL: return "libnccl.so.2 not loadable";
     case B200V_E_NOMEM: return "host allocation failed";
+    case B200V_E_TOOLARGE: return "size exceeds the fixed capacity of the no-allocation entry point";
     default: return "unknown b200v error";
     }
 }

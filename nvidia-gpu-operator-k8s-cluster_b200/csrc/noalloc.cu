@@ -1,0 +1,102 @@
+// noalloc.cu — b200v_vectoradd_noalloc: the host-buffer vectorAdd for callers that must not
+// allocate device memory.
+//
+// Who that is: a validator re-run as a health probe on a node whose GPU is already in service.
+// There the HBM may be almost entirely committed to the tenant's job, so a cudaMalloc of staging
+// buffers can fail (and the probe would then report a healthy GPU as broken), and cudaMalloc /
+// cudaFree also synchronise the device, which stalls the tenant's streams for the duration.  The
+// regular entry point (b200v_vectoradd) allocates a ring of staging slots and creates streams and
+// events on first use; this one touches none of that.  Its device staging lives in the
+// file-scope array below, reserved when the library's module is loaded on a GPU and held until
+// the process exits, so the probe can always run and never asks the allocator for anything.
+//
+// What the caller gives up: the problem size is capped at B200V_NOALLOC_MAX_ELEMS elements per
+// vector (larger n is refused with B200V_E_TOOLARGE, nothing is computed), there is no
+// transfer/kernel overlap (one stream, three copies and one launch in order), and there is one
+// staging array per GPU per process, shared by every call: two calls that overlap in time on the
+// same GPU (two host threads, or two streams) race on it and produce garbage.  Serialise them.
+//
+// Stale contents: the array keeps whatever the previous call left.  Nothing here needs it to
+// start at zero — every element the kernel reads was written by this call's own two
+// host-to-device copies, and every element copied back was written by this call's kernel — so no
+// clearing is done.
+//
+// First call on each GPU: the entry point itself does the one-time set-up for that GPU (with the
+// GPU current, it asks the runtime for the device address of the array and remembers it).  Make
+// that first call before you begin any stream capture; later calls only reuse the address.
+#include <mutex>
+
+#include "ew_kernels.cuh"
+
+// 3 vectors x 2^20 floats x 4 B = 12 MiB of HBM per GPU that loads this library.
+static __device__ __align__(256) float g_noalloc_scratch[3 * B200V_NOALLOC_MAX_ELEMS];
+
+namespace {
+
+// In host code the name g_noalloc_scratch is only a handle for the runtime, not an address the
+// GPU understands; the device address is looked up once per device and kept here.
+constexpr int kMaxDevices = 64;
+float *g_scratch_addr[kMaxDevices];
+std::mutex g_setup_mu;
+
+// Must be called with `dev` current.
+int scratch_for_device(int dev, float **out) {
+    std::lock_guard<std::mutex> lock(g_setup_mu);
+    if (!g_scratch_addr[dev]) {
+        float *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            return (int)e;
+        }
+        g_scratch_addr[dev] = p;
+    }
+    *out = g_scratch_addr[dev];
+    return B200V_OK;
+}
+
+#define NOALLOC_CUDA(expr)                                 \
+    do {                                                   \
+        cudaError_t e__ = (expr);                          \
+        if (e__ != cudaSuccess) {                          \
+            (void)cudaGetLastError();                      \
+            return (int)e__;                               \
+        }                                                  \
+    } while (0)
+
+}  // namespace
+
+extern "C" int b200v_vectoradd_noalloc(int dev, const float *hA, const float *hB, float *hC, size_t n,
+                                       void *stream) {
+    if (n > (size_t)B200V_NOALLOC_MAX_ELEMS) return B200V_E_TOOLARGE;
+    if (n > 0 && (!hA || !hB || !hC)) return B200V_E_BADARG;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        return B200V_E_NODEVICE;
+    }
+    if (dev < 0 || dev >= count || dev >= kMaxDevices) return B200V_E_BADARG;
+    NOALLOC_CUDA(cudaSetDevice(dev));
+    float *base = nullptr;
+    int rc = scratch_for_device(dev, &base);   // first call on a device: the one-time address lookup
+    if (rc != B200V_OK) return rc;
+    if (n == 0) return B200V_OK;
+
+    cudaStream_t st = (cudaStream_t)stream;
+    float *dA = base;
+    float *dB = base + (size_t)B200V_NOALLOC_MAX_ELEMS;
+    float *dC = base + 2 * (size_t)B200V_NOALLOC_MAX_ELEMS;
+    NOALLOC_CUDA(cudaMemcpyAsync(dA, hA, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    NOALLOC_CUDA(cudaMemcpyAsync(dB, hB, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    // Same kernel as the default path of b200v_vectoradd: one 2048-element tile per CTA, 256-bit
+    // accesses (the three sub-arrays start 4 MiB apart, so all are 32-byte aligned).
+    constexpr int kBlock = 256, kVec = 8;
+    const unsigned grid = (unsigned)((n + (size_t)kBlock * kVec - 1) / ((size_t)kBlock * kVec));
+    b200v::ew_vec_kernel<B200V_OP_VECTORADD, kVec, 1, kBlock, b200v::LD_PLAIN, b200v::ST_PLAIN>
+        <<<grid, kBlock, 0, st>>>(dC, dA, dB, 0.0f, n);
+    NOALLOC_CUDA(cudaGetLastError());
+    NOALLOC_CUDA(cudaMemcpyAsync(hC, dC, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    NOALLOC_CUDA(cudaStreamSynchronize(st));
+    return B200V_OK;
+}
