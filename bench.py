@@ -314,8 +314,17 @@ def main():
         if rank == 0:
             uid.copy_(torch.frombuffer(bytearray(capi.nccl_unique_id()), dtype=torch.uint8))
         dist.broadcast(uid, src=0)
-        rows = capi.allreduce_probe_rank(dev, rank, world, bytes(uid.cpu().numpy().tobytes()),
-                                         min_bytes=1 << 20, max_bytes=1 << 30, warmup=5, iters=20)
+        # NCCL announces its version on stdout when a communicator is created; stdout must carry
+        # the one JSON line only, so the probe runs with fd 1 pointed at stderr.
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            rows = capi.allreduce_probe_rank(dev, rank, world, bytes(uid.cpu().numpy().tobytes()),
+                                             min_bytes=1 << 20, max_bytes=1 << 30, warmup=5, iters=20)
+        finally:
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
         ms = torch.tensor([r.best_ms for r in rows], dtype=torch.float64, device="cuda")
         badrows = torch.tensor([float(r.mismatches) for r in rows], dtype=torch.float64, device="cuda")
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)

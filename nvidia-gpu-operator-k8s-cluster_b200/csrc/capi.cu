@@ -3,6 +3,7 @@
 // no usable device every compute entry point returns B200V_E_NODEVICE or the CUDA error.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -153,8 +154,26 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
     if (n == 0) return B200V_OK;
     DeviceCtx &c = *g.c;
 
-    const size_t chunk = std::min(n, kChunkElems);
-    const size_t nchunks = (n + chunk - 1) / chunk;
+    // B200V_CHUNK_LOG2 overrides the chunk size (elements, log2) for transfer tuning runs.
+    static const size_t chunk_cap = [] {
+        const char *e = std::getenv("B200V_CHUNK_LOG2");
+        const int lg = e && *e ? std::atoi(e) : 0;
+        return (lg >= 10 && lg <= 30) ? (size_t)1 << lg : kChunkElems;
+    }();
+    const size_t chunk = std::min(n, chunk_cap);
+    // Chunk schedule: full-size chunks, then a geometric taper (each chunk at most half of what is
+    // left, down to kMinChunkElems).  The H2D stream is the bottleneck and runs back to back from
+    // t = 0, so the call ends one kernel + one D2H after the LAST chunk lands: keeping that last
+    // chunk small removes ~1 ms (one 64 MiB D2H) from a 2^28-element call.
+    std::vector<std::pair<size_t, size_t>> sched;   // (first element, length)
+    for (size_t at = 0; at < n;) {
+        const size_t left = n - at;
+        size_t len = std::min(chunk, std::max(kMinChunkElems, left / 2));
+        if (len > left) len = left;
+        sched.emplace_back(at, len);
+        at += len;
+    }
+    const size_t nchunks = sched.size();
     rc = ensure_slots(c, chunk);
     if (rc != B200V_OK) return rc;
     while (c.k_ev.size() < 2 * nchunks) {
@@ -169,7 +188,7 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
     B200V_CUDA(cudaStreamWaitEvent(c.s_out, c.t_begin, 0));
     for (size_t k = 0; k < nchunks; ++k) {
         const int slot = (int)(k % kSlots);
-        const size_t lo = k * chunk, len = std::min(chunk, n - lo);
+        const size_t lo = sched[k].first, len = sched[k].second;
         // inputs of this slot are free once the kernel that read them (chunk k - kSlots) is done
         if (k >= (size_t)kSlots) B200V_CUDA(cudaStreamWaitEvent(c.s_in, c.k_done[slot], 0));
         if (k == 0) B200V_CUDA(cudaEventRecord(c.h2d_first, c.s_in));

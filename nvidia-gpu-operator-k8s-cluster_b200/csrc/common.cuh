@@ -22,7 +22,10 @@ namespace b200v {
 
 // Host-path pipeline geometry: the transfers are cut into chunks that ride a ring of device
 // slots, so device memory use is bounded whatever n is (3 arrays x SLOTS x CHUNK_ELEMS x 4 B).
-constexpr size_t kChunkElems = (size_t)1 << 22;   // 16 MiB per array per chunk
+// 64 MiB chunks measured best on PCIe Gen5 x16 (tools/e2e_tune.py: 2^22 -> 44.6 ms, 2^24 -> 42.8 ms,
+// 2^26 -> 45.3 ms for a 2^28-element call); the ring then holds 3 x 3 x 64 MiB = 576 MiB.
+constexpr size_t kChunkElems = (size_t)1 << 24;
+constexpr size_t kMinChunkElems = (size_t)1 << 20;   // tail of the taper (4 MiB)
 constexpr int kSlots = 3;
 
 struct DeviceCtx {

@@ -170,6 +170,157 @@ ew_vec_kernel(float *__restrict__ dst, const float *__restrict__ x, const float 
     }
 }
 
+// ---- the one-tile-per-CTA kernel ---------------------------------------------------------------------
+// The measured winner is "one tile per CTA" (the hardware block scheduler balances the SMs), and
+// for that shape the grid-stride loop above is dead weight: its trip-count division and the
+// ragged-end ownership test cost ~80 scalar instructions before the first load issues, in each of
+// the 131072 CTAs of a 2^28-element launch.  This kernel is that shape with nothing else in it:
+// CTA b owns elements [b*TILE*VEC, (b+1)*TILE*VEC); every CTA but the last takes the unguarded
+// path.  Launch with grid = ceil(n / (BLOCK*UNROLL*VEC)) (>= 1).  MINB is the occupancy hint.
+template <int OP, int VEC, int UNROLL, int BLOCK, int LDPOL, int STPOL, int MINB = 1>
+__global__ void __launch_bounds__(BLOCK, MINB)
+ew_tile_kernel(float *__restrict__ dst, const float *__restrict__ x, const float *__restrict__ y,
+               float s, size_t n) {
+    constexpr bool needs_y = ew_traits<OP>::needs_y;
+    constexpr size_t TILE = (size_t)BLOCK * UNROLL;          // vectors per tile
+    const uint64_t pol = (LDPOL == LD_NC_NA_EF && VEC == 4) ? make_evict_first_policy() : 0;
+    const size_t v0 = (size_t)blockIdx.x * TILE + threadIdx.x;
+    const size_t e0 = v0 * VEC;
+
+    if (((size_t)blockIdx.x + 1) * TILE * VEC <= n) {
+        fvec<VEC> a[UNROLL], b[UNROLL];
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) a[j] = ew_load<VEC, LDPOL>(x + e0 + (size_t)j * BLOCK * VEC, pol);
+        if constexpr (needs_y) {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) b[j] = ew_load<VEC, LDPOL>(y + e0 + (size_t)j * BLOCK * VEC, pol);
+        }
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            fvec<VEC> r;
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) r.v[k] = ew_apply<OP>(a[j].v[k], needs_y ? b[j].v[k] : 0.0f, s);
+            ew_store<VEC, STPOL>(dst + e0 + (size_t)j * BLOCK * VEC, r);
+        }
+        return;
+    }
+    // last CTA: guarded vectors, then the n % VEC scalar elements
+    const size_t n_vec = n / VEC;
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+        const size_t v = v0 + (size_t)j * BLOCK;
+        if (v < n_vec) {
+            fvec<VEC> a = ew_load<VEC, LDPOL>(x + v * VEC, pol), b, r;
+            if constexpr (needs_y) b = ew_load<VEC, LDPOL>(y + v * VEC, pol);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) r.v[k] = ew_apply<OP>(a.v[k], needs_y ? b.v[k] : 0.0f, s);
+            ew_store<VEC, STPOL>(dst + v * VEC, r);
+        }
+    }
+    const size_t i = n_vec * VEC + threadIdx.x;
+    if (threadIdx.x < VEC && i < n) dst[i] = ew_apply<OP>(x[i], needs_y ? y[i] : 0.0f, s);
+}
+
+// ---- persistent kernel with hardware work stealing (cluster launch control) ---------------------------
+// Blackwell's answer to "persistent CTAs, but dynamically balanced": the grid is still one CTA per
+// tile, but a running CTA that finishes its tile asks the hardware scheduler to cancel a CTA that
+// has not started yet (clusterlaunchcontrol.try_cancel) and processes that CTA's tile itself.  The
+// CTA-launch cost is paid ~once per SM slot instead of once per tile, and unlike a static
+// grid-stride partition the work still flows to whichever SM is free.  Launch exactly like
+// ew_tile_kernel.  Thread 0 issues the request one tile ahead; the 16-byte response lands in
+// shared memory and completes an mbarrier all threads wait on.
+template <int OP, int VEC, int UNROLL, int BLOCK, int LDPOL, int STPOL, int MINB = 1>
+__global__ void __launch_bounds__(BLOCK, MINB)
+ew_clc_kernel(float *__restrict__ dst, const float *__restrict__ x, const float *__restrict__ y,
+              float s, size_t n) {
+    constexpr bool needs_y = ew_traits<OP>::needs_y;
+    constexpr size_t TILE = (size_t)BLOCK * UNROLL;
+    __shared__ __align__(16) uint4 clc_resp[2];
+    __shared__ __align__(8) uint64_t clc_bar[2];
+    const uint64_t pol = (LDPOL == LD_NC_NA_EF && VEC == 4) ? make_evict_first_policy() : 0;
+
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((uint32_t)__cvta_generic_to_shared(&clc_bar[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((uint32_t)__cvta_generic_to_shared(&clc_bar[1])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto request = [&](int slot) {      // thread 0 only
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&clc_bar[slot]);
+        const uint32_t resp = (uint32_t)__cvta_generic_to_shared(&clc_resp[slot]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], 16;" :: "r"(bar) : "memory");
+        asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+                     :: "r"(resp), "r"(bar) : "memory");
+    };
+
+    unsigned tile = blockIdx.x;
+    int slot = 0;
+    uint32_t phase[2] = {0, 0};
+    if (threadIdx.x == 0) request(0);
+    for (;;) {
+        // ---- process `tile` ----
+        const size_t v0 = (size_t)tile * TILE + threadIdx.x;
+        const size_t e0 = v0 * VEC;
+        if (((size_t)tile + 1) * TILE * VEC <= n) {
+            fvec<VEC> a[UNROLL], b[UNROLL];
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) a[j] = ew_load<VEC, LDPOL>(x + e0 + (size_t)j * BLOCK * VEC, pol);
+            if constexpr (needs_y) {
+#pragma unroll
+                for (int j = 0; j < UNROLL; ++j) b[j] = ew_load<VEC, LDPOL>(y + e0 + (size_t)j * BLOCK * VEC, pol);
+            }
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                fvec<VEC> r;
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) r.v[k] = ew_apply<OP>(a[j].v[k], needs_y ? b[j].v[k] : 0.0f, s);
+                ew_store<VEC, STPOL>(dst + e0 + (size_t)j * BLOCK * VEC, r);
+            }
+        } else {
+            const size_t n_vec = n / VEC;
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const size_t v = v0 + (size_t)j * BLOCK;
+                if (v < n_vec) {
+                    fvec<VEC> a = ew_load<VEC, LDPOL>(x + v * VEC, pol), b, r;
+                    if constexpr (needs_y) b = ew_load<VEC, LDPOL>(y + v * VEC, pol);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) r.v[k] = ew_apply<OP>(a.v[k], needs_y ? b.v[k] : 0.0f, s);
+                    ew_store<VEC, STPOL>(dst + v * VEC, r);
+                }
+            }
+            const size_t i = n_vec * VEC + threadIdx.x;
+            if (threadIdx.x < VEC && i < n) dst[i] = ew_apply<OP>(x[i], needs_y ? y[i] : 0.0f, s);
+        }
+        // ---- next tile: the response requested while this one was in flight ----
+        {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&clc_bar[slot]);
+            asm volatile(
+                "{\n.reg .pred p;\nCLCW_%=:\n"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                "@p bra CLCD_%=;\nbra CLCW_%=;\nCLCD_%=:\n}\n" :: "r"(bar), "r"(phase[slot]) : "memory");
+            phase[slot] ^= 1;
+        }
+        const uint32_t resp = (uint32_t)__cvta_generic_to_shared(&clc_resp[slot]);
+        uint32_t ok = 0, next = 0;
+        asm volatile(
+            "{\n.reg .pred p;\n.reg .b128 r;\n"
+            "ld.shared.b128 r, [%2];\n"
+            "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "@p clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %1, r;\n"
+            "}\n" : "=r"(ok), "=r"(next) : "r"(resp) : "memory");
+        if (!ok) break;
+        tile = next;
+        // every thread has read this slot's response before it is reused two rounds from now
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        slot ^= 1;
+        if (threadIdx.x == 0) request(slot);
+    }
+}
+
 // ---- scalar kernels --------------------------------------------------------------------------------
 // (1) The sample's own shape: one element per thread, bounds-checked.  Used as
 //     the in-library cross-check of the vector kernels and for the sampleshape entry point.

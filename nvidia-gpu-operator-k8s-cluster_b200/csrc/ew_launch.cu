@@ -53,15 +53,28 @@ struct Variant {
      ew_bulk_smem_bytes<B200V_OP_VECTORADD, TILE_F, STAGES>(),                         \
      ew_bulk_smem_bytes<B200V_OP_TRIAD_UNFUSED, TILE_F, STAGES>()}
 
+#define EW_TILE_ROW(K, VEC, UNROLL, BLOCK, MINB)                                               \
+    {K<B200V_OP_COPY, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>,                             \
+     K<B200V_OP_SCALE, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>,                            \
+     K<B200V_OP_ADD, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>,                              \
+     K<B200V_OP_TRIAD, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>,                            \
+     K<B200V_OP_VECTORADD, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>,                        \
+     K<B200V_OP_TRIAD_UNFUSED, VEC, UNROLL, BLOCK, LD_PLAIN, ST_PLAIN, MINB>}
+
 // Variant 0 is the default for 32-byte aligned data, variant 1 for data that is only 16-byte
-// aligned.  Measured on a B200 at n = 2^28 (profiles/r01_tune.md): one tile per CTA ("oneshot",
-// the hardware block scheduler balances the SMs) beats a static grid-stride partition by 3-9 %,
-// 256-bit accesses beat 128-bit by ~1 %, and the default cache policy beats evict-first by ~1 %.
-// The persistent grid-stride and TMA-bulk shapes stay compiled for A/B runs (B200V_EW_VARIANT).
+// aligned.  Measured on a B200 at n = 2^28 (profiles/README.md): every good shape plateaus at the
+// same ~7.05 TB/s (DRAM-bound); what loses is (a) a static grid-stride partition over persistent
+// CTAs (3-9 %: nothing rebalances the per-SM speed spread), (b) many small tiles in flight (8 KiB
+// tiles at full occupancy: -1.3 %, DRAM page locality), (c) streaming cache hints (-1 %).  The
+// default is therefore the lean one-tile-per-CTA kernel with 1024-thread CTAs (32 KiB contiguous
+// per array per CTA, 2 CTAs per SM).  ctas_per_sm == 0 means "one CTA per tile".
+// The other shapes stay compiled for A/B runs (B200V_EW_VARIANT): the grid-stride kernel in its
+// one-shot and persistent forms, the cluster-launch-control work-stealing kernel and the TMA ring.
 Variant g_variants[] = {
+    {"t8u1b1024", 8, 1, 1024, false, 0, 0, 0, EW_TILE_ROW(ew_tile_kernel, 8, 1, 1024, 2), {}},
+    {"t4u2b1024", 4, 2, 1024, false, 0, 0, 0, EW_TILE_ROW(ew_tile_kernel, 4, 2, 1024, 2), {}},
     {"v8u1b256-oneshot", 8, 1, 256, false, 0, 0, 0, EW_VEC_ROW(8, 1, 256, LD_PLAIN, ST_PLAIN), {}},
-    {"v4u2b256-oneshot", 4, 2, 256, false, 0, 0, 0, EW_VEC_ROW(4, 2, 256, LD_PLAIN, ST_PLAIN), {}},
-    {"v8u2b1024-oneshot", 8, 2, 1024, false, 0, 0, 0, EW_VEC_ROW(8, 2, 1024, LD_PLAIN, ST_PLAIN), {}},
+    {"clc8u1b1024", 8, 1, 1024, false, 0, 0, 0, EW_TILE_ROW(ew_clc_kernel, 8, 1, 1024, 2), {}},
     {"v8u2b256-persist8", 8, 2, 256, false, 0, 0, 8, EW_VEC_ROW(8, 2, 256, LD_NC_NA_EF, ST_CS), {}},
     {"v4u4b256-persist8", 4, 4, 256, false, 0, 0, 8, EW_VEC_ROW(4, 4, 256, LD_NC_NA_EF, ST_CS), {}},
     {"bulk2048s3b128", 4, 0, 128, true, 2048, 0, 2, EW_BULK_ROW(2048, 3, 128), EW_BULK_SMEM(2048, 3)},

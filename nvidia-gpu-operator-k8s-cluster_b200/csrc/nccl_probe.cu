@@ -6,6 +6,7 @@
 // exact whatever order the ring, tree or NVSwitch reduction adds in, and the result is checked
 // bit for bit against the closed form on the device.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 #include <mutex>
@@ -28,6 +29,12 @@ struct NcclApi {
                               cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
+    // optional (NCCL >= 2.19): buffers from NCCL's own allocator, registered with the communicator,
+    // let NVLS / copy-engine paths work on the user buffer directly instead of staging through FIFOs
+    ncclResult_t (*MemAlloc)(void **, size_t) = nullptr;
+    ncclResult_t (*MemFree)(void *) = nullptr;
+    ncclResult_t (*CommRegister)(ncclComm_t, void *, size_t, void **) = nullptr;
+    ncclResult_t (*CommDeregister)(ncclComm_t, void *) = nullptr;
 };
 
 NcclApi g_nccl;
@@ -51,6 +58,10 @@ const NcclApi *nccl() {
                   sym(h, "ncclCommInitRank", a.CommInitRank) && sym(h, "ncclCommInitAll", a.CommInitAll) &&
                   sym(h, "ncclCommDestroy", a.CommDestroy) && sym(h, "ncclAllReduce", a.AllReduce) &&
                   sym(h, "ncclGroupStart", a.GroupStart) && sym(h, "ncclGroupEnd", a.GroupEnd);
+        sym(h, "ncclMemAlloc", a.MemAlloc);
+        sym(h, "ncclMemFree", a.MemFree);
+        sym(h, "ncclCommRegister", a.CommRegister);
+        sym(h, "ncclCommDeregister", a.CommDeregister);
         if (ok) g_nccl = a;
     });
     return g_nccl.handle ? &g_nccl : nullptr;
@@ -96,6 +107,9 @@ struct Rank {
     ncclComm_t comm = nullptr;
     cudaStream_t st = nullptr;
     float *buf = nullptr;
+    size_t buf_bytes = 0;
+    bool nccl_mem = false;        // buf came from ncclMemAlloc
+    void *reg_handle = nullptr;   // ncclCommRegister handle
     unsigned long long *d_bad = nullptr;
     int sm_count = 0;
     std::vector<cudaEvent_t> ev;
@@ -106,24 +120,48 @@ void destroy_ranks(const NcclApi *api, std::vector<Rank> &rs) {
         if (r.dev < 0) continue;
         cudaSetDevice(r.dev);
         if (r.st) cudaStreamSynchronize(r.st);
+        if (r.comm && r.reg_handle && api->CommDeregister) api->CommDeregister(r.comm, r.reg_handle);
         if (r.comm) api->CommDestroy(r.comm);
         for (cudaEvent_t e : r.ev) cudaEventDestroy(e);
-        if (r.buf) cudaFree(r.buf);
+        if (r.buf && r.nccl_mem) api->MemFree(r.buf);
+        else if (r.buf) cudaFree(r.buf);
         if (r.d_bad) cudaFree(r.d_bad);
         if (r.st) cudaStreamDestroy(r.st);
     }
     rs.clear();
 }
 
-int setup_rank(Rank &r, size_t max_bytes, int iters) {
+bool plain_buffers() {
+    const char *e = std::getenv("B200V_NCCL_PLAIN_BUFFERS");
+    return e && *e && *e != '0';
+}
+
+int setup_rank(const NcclApi *api, Rank &r, size_t max_bytes, int iters) {
     B200V_CUDA(cudaSetDevice(r.dev));
     B200V_CUDA(cudaDeviceGetAttribute(&r.sm_count, cudaDevAttrMultiProcessorCount, r.dev));
     B200V_CUDA(cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
-    B200V_CUDA(cudaMalloc(&r.buf, max_bytes));
+    r.buf_bytes = max_bytes;
+    if (api->MemAlloc && api->MemFree && !plain_buffers()) {
+        void *p = nullptr;
+        if (api->MemAlloc(&p, max_bytes) == ncclSuccess && p) {
+            r.buf = (float *)p;
+            r.nccl_mem = true;
+        }
+    }
+    if (!r.buf) B200V_CUDA(cudaMalloc(&r.buf, max_bytes));
     B200V_CUDA(cudaMalloc(&r.d_bad, 8));
     r.ev.resize((size_t)iters * 2);
     for (auto &e : r.ev) B200V_CUDA(cudaEventCreate(&e));
     return B200V_OK;
+}
+
+// After the communicator exists: register the buffer with it (best effort; the probe is still
+// valid unregistered, only slower).
+void register_buffer(const NcclApi *api, Rank &r) {
+    if (!r.nccl_mem || !api->CommRegister || !api->CommDeregister) return;
+    cudaSetDevice(r.dev);
+    void *h = nullptr;
+    if (api->CommRegister(r.comm, r.buf, r.buf_bytes, &h) == ncclSuccess) r.reg_handle = h;
 }
 
 int grid_for(const Rank &r, size_t n) {
@@ -268,12 +306,15 @@ int b200v_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t ma
     for (int i = 0; i < ndev; ++i) {
         rs[i].dev = devs[i];
         rs[i].rank = i;
-        rc = setup_rank(rs[i], max_bytes, iters);
+        rc = setup_rank(api, rs[i], max_bytes, iters);
         if (rc != B200V_OK) return rc;
     }
     std::vector<ncclComm_t> comms((size_t)ndev);
     B200V_NCCL(api->CommInitAll(comms.data(), ndev, devs), (b200v_ar_row *)nullptr);
-    for (int i = 0; i < ndev; ++i) rs[i].comm = comms[i];
+    for (int i = 0; i < ndev; ++i) {
+        rs[i].comm = comms[i];
+        register_buffer(api, rs[i]);
+    }
     return sweep(api, rs, ndev, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
 }
 
@@ -300,11 +341,12 @@ int b200v_allreduce_probe_rank(int dev, int rank, int nranks,
     } cleanup{api, rs};
     rs[0].dev = dev;
     rs[0].rank = rank;
-    rc = setup_rank(rs[0], max_bytes, iters);
+    rc = setup_rank(api, rs[0], max_bytes, iters);
     if (rc != B200V_OK) return rc;
     ncclUniqueId u;
     std::memcpy(&u, id, sizeof(u));
     B200V_NCCL(api->CommInitRank(&rs[0].comm, nranks, u, rank), (b200v_ar_row *)nullptr);
+    register_buffer(api, rs[0]);
     return sweep(api, rs, nranks, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
 }
 

@@ -89,8 +89,8 @@ extern "C" int b200v_vectoradd_noalloc(int dev, const float *hA, const float *hB
     float *dC = base + 2 * (size_t)B200V_NOALLOC_MAX_ELEMS;
     NOALLOC_CUDA(cudaMemcpyAsync(dA, hA, n * sizeof(float), cudaMemcpyHostToDevice, st));
     NOALLOC_CUDA(cudaMemcpyAsync(dB, hB, n * sizeof(float), cudaMemcpyHostToDevice, st));
-    // Same kernel as the default path of b200v_vectoradd: one 2048-element tile per CTA, 256-bit
-    // accesses (the three sub-arrays start 4 MiB apart, so all are 32-byte aligned).
+    // The library's 256-bit vector kernel at one 2048-element tile per CTA (the three sub-arrays
+    // start 4 MiB apart, so all are 32-byte aligned); results are identical on every kernel shape.
     constexpr int kBlock = 256, kVec = 8;
     const unsigned grid = (unsigned)((n + (size_t)kBlock * kVec - 1) / ((size_t)kBlock * kVec));
     b200v::ew_vec_kernel<B200V_OP_VECTORADD, kVec, 1, kBlock, b200v::LD_PLAIN, b200v::ST_PLAIN>

@@ -407,7 +407,17 @@ int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     std::vector<b200v_ar_row> rows(64);
     int nrows = 0;
     const size_t lo = (size_t)1 << env_int("B200V_MIN_LOG2", 10), hi = (size_t)1 << env_int("B200V_MAX_LOG2", 30);
+    // NCCL prints its version banner on stdout at communicator creation; keep stdout for the JSON
+    // rows by pointing fd 1 at stderr for the duration of the call.
+    std::fflush(nullptr);
+    const int saved_fd = ::dup(1);
+    if (saved_fd >= 0) ::dup2(2, 1);
     rc = api.allreduce_probe(use, devs.data(), lo, hi, 5, 20, rows.data(), (int)rows.size(), &nrows);
+    std::fflush(nullptr);
+    if (saved_fd >= 0) {
+        ::dup2(saved_fd, 1);
+        ::close(saved_fd);
+    }
     int failures = rc != B200V_OK ? 1 : 0;
     if (rc != B200V_OK) std::fprintf(err, "nccl probe failed: %s\n", api.strerror(rc));
     const double min_busbw = std::atof(env_or("B200V_MIN_BUSBW_GBS", "0").c_str());

@@ -2,7 +2,7 @@
 // runs on and prints one CSV row per (kernel variant, grid) so the product defaults in
 // csrc/ew_launch.cu can be chosen from measurements.  Development tool, not shipped in the image.
 //
-//   b200v-tune [log2_n=28] [iters=10] [quick]
+//   b200v-tune [log2_n=28] [iters=10] [quick|tiles]
 //
 // Every row is checked against the scalar sample-shape kernel before it is timed.
 #include <algorithm>
@@ -35,6 +35,7 @@ struct Cfg {
     size_t tile_elems;   // elements per tile (vec: BLOCK*UNROLL*VEC; bulk: TILE_F)
     size_t smem;
     bool bulk;
+    bool oneshot_only = false;   // ew_tile_kernel / ew_clc_kernel: grid is always one CTA per tile
 };
 
 static std::vector<Cfg> g_cfgs;
@@ -62,6 +63,30 @@ static void reg_bulk() {
                       ew_bulk_smem_bytes<OP, TILE_F, STAGES>(), true});
 }
 
+template <int OP, int VEC, int UNROLL, int BLOCK, int LD, int ST, int MINB>
+static void reg_tile() {
+    char buf[128];
+    std::snprintf(buf, sizeof buf, "tile%d_u%d_b%d_m%d_%s_%s", VEC * 32, UNROLL, BLOCK, MINB, ld_name(LD), st_name(ST));
+    g_cfgs.push_back({buf, OP, ew_tile_kernel<OP, VEC, UNROLL, BLOCK, LD, ST, MINB>, BLOCK,
+                      (size_t)BLOCK * UNROLL * VEC, 0, false, true});
+    std::snprintf(buf, sizeof buf, "clc%d_u%d_b%d_m%d_%s_%s", VEC * 32, UNROLL, BLOCK, MINB, ld_name(LD), st_name(ST));
+    g_cfgs.push_back({buf, OP, ew_clc_kernel<OP, VEC, UNROLL, BLOCK, LD, ST, MINB>, BLOCK,
+                      (size_t)BLOCK * UNROLL * VEC, 0, false, true});
+}
+
+template <int OP, int LD, int ST>
+static void reg_tile_shapes() {
+    reg_tile<OP, 8, 1, 256, LD, ST, 1>(); reg_tile<OP, 8, 1, 256, LD, ST, 8>();
+    reg_tile<OP, 8, 2, 256, LD, ST, 1>(); reg_tile<OP, 8, 2, 256, LD, ST, 4>();
+    reg_tile<OP, 8, 4, 256, LD, ST, 1>(); reg_tile<OP, 8, 1, 512, LD, ST, 1>();
+    reg_tile<OP, 8, 1, 512, LD, ST, 4>(); reg_tile<OP, 8, 2, 512, LD, ST, 1>();
+    reg_tile<OP, 8, 1, 1024, LD, ST, 1>(); reg_tile<OP, 8, 1, 1024, LD, ST, 2>();
+    reg_tile<OP, 8, 2, 1024, LD, ST, 1>(); reg_tile<OP, 8, 1, 128, LD, ST, 1>();
+    reg_tile<OP, 8, 1, 128, LD, ST, 16>(); reg_tile<OP, 8, 2, 128, LD, ST, 1>();
+    reg_tile<OP, 4, 2, 256, LD, ST, 1>(); reg_tile<OP, 4, 4, 256, LD, ST, 1>();
+    reg_tile<OP, 4, 2, 512, LD, ST, 1>(); reg_tile<OP, 4, 1, 256, LD, ST, 8>();
+}
+
 template <int OP, int LD, int ST>
 static void reg_vec_shapes() {
     reg_vec<OP, 4, 1, 256, LD, ST>(); reg_vec<OP, 4, 2, 256, LD, ST>();
@@ -84,7 +109,18 @@ static void reg_bulk_shapes() {
     reg_bulk<OP, 8192, 4, 512>(); reg_bulk<OP, 16384, 3, 512>();
 }
 
-static void register_all(bool quick) {
+static void register_all(bool quick, bool tiles_only) {
+    reg_tile_shapes<B200V_OP_VECTORADD, LD_PLAIN, ST_PLAIN>();
+    reg_tile_shapes<B200V_OP_VECTORADD, LD_NC_NA, ST_PLAIN>();
+    reg_tile_shapes<B200V_OP_COPY, LD_PLAIN, ST_PLAIN>();
+    reg_tile_shapes<B200V_OP_TRIAD, LD_PLAIN, ST_PLAIN>();
+    reg_tile_shapes<B200V_OP_SCALE, LD_PLAIN, ST_PLAIN>();
+    reg_tile_shapes<B200V_OP_ADD, LD_PLAIN, ST_PLAIN>();
+    if (tiles_only) {   // keep two reference rows from the first sweep
+        reg_vec<B200V_OP_VECTORADD, 8, 1, 256, LD_PLAIN, ST_PLAIN>();
+        reg_vec<B200V_OP_VECTORADD, 8, 2, 1024, LD_PLAIN, ST_PLAIN>();
+        return;
+    }
     reg_vec_shapes<B200V_OP_VECTORADD, LD_NC_NA_EF, ST_CS>();
     reg_bulk_shapes<B200V_OP_VECTORADD>();
     if (!quick) {
@@ -118,6 +154,7 @@ int main(int argc, char **argv) {
     const int log2n = argc > 1 ? std::atoi(argv[1]) : 28;
     const int iters = argc > 2 ? std::atoi(argv[2]) : 10;
     const bool quick = argc > 3 && std::strcmp(argv[3], "quick") == 0;
+    const bool tiles_only = argc > 3 && std::strcmp(argv[3], "tiles") == 0;
     const size_t n = (size_t)1 << log2n;
 
     cudaDeviceProp prop;
@@ -134,7 +171,7 @@ int main(int argc, char **argv) {
     fill_hash_kernel<<<sms * 8, 256>>>(y, n, 0xB201);
     CK(cudaDeviceSynchronize());
 
-    register_all(quick);
+    register_all(quick, tiles_only);
     std::vector<cudaEvent_t> ev((size_t)iters * 2);
     for (auto &e : ev) CK(cudaEventCreate(&e));
 
@@ -180,6 +217,7 @@ int main(int argc, char **argv) {
         for (int m : grid_mults) {
             if (m > occ) continue;                  // more CTAs than fit is just a second wave
             if (m == 0 && c.bulk) continue;         // the bulk ring needs several tiles per CTA
+            if (m != 0 && c.oneshot_only) continue;
             const size_t g = m == 0 ? tiles : std::min(tiles, (size_t)sms * m);
             CK(cudaMemsetAsync(d, 0xFF, n * 4));
             c.fn<<<(unsigned)g, c.block, c.smem>>>(d, x, y, 3.0f, n);

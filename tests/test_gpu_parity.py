@@ -65,7 +65,7 @@ def test_vectoradd_host_multichunk_pipeline(capi, oracle, gpu):
     want = oracle.vadd(A, B, threads=8)
     C = np.zeros(n, np.float32)
     t = capi.vectoradd(A, B, C)
-    assert t.chunks == 6 and t.kernel_launches == 6
+    assert t.chunks > 3 and t.kernel_launches == t.chunks          # more chunks than ring slots
     assert same_bytes(C, want)
     pa, pb, pc = capi.PinnedArray(n), capi.PinnedArray(n), capi.PinnedArray(n)
     pa.array[:] = A
@@ -217,7 +217,7 @@ print("VARIANT_OK" if ok else "VARIANT_BAD")
 """
 
 
-@pytest.mark.parametrize("variant", ["v8u1b256-oneshot", "v4u2b256-oneshot", "v8u2b1024-oneshot",
+@pytest.mark.parametrize("variant", ["t8u1b1024", "t4u2b1024", "v8u1b256-oneshot", "clc8u1b1024",
                                      "v8u2b256-persist8", "v4u4b256-persist8", "bulk2048s3b128"])
 def test_kernel_variants(gpu, variant):
     env = dict(os.environ, B200V_EW_VARIANT=variant)
@@ -271,7 +271,7 @@ def test_cfg1_host_path_full_size(capi, oracle, gpu):
     lib.oracle_fill_hash_mt(pa.array.ctypes.data_as(f32p), n, SEED, threads)
     lib.oracle_fill_hash_mt(pb.array.ctypes.data_as(f32p), n, SEED + oracle.SEED_Y_OFFSET, threads)
     t = capi.vectoradd(pa.array, pb.array, pc.array)
-    assert t.chunks == 64
+    assert t.chunks >= 16 and t.kernel_launches == t.chunks
     want = oracle.vadd(pa.array, pb.array, threads=threads)
     assert same_bytes(pc.array, want)
     for p in (pa, pb, pc):
@@ -296,3 +296,57 @@ def test_bad_arguments(capi, gpu):
     assert ei.value.code == capi.E_BADARG
     info = capi.device_info(0)
     assert info.sm_count > 0 and info.l2_bytes > 0 and info.hbm_bytes > 0 and info.cc_major >= 10
+
+
+# ---- NVLink probe and the real executables ---------------------------------------------------------
+
+def test_allreduce_probe_single_device(capi, gpu):
+    """One rank: the all-reduce is the identity, which still exercises communicator set-up, the
+    fill/check kernels and the row bookkeeping on a 1-GPU box."""
+    assert capi.nccl_version() >= 22000
+    rows = capi.allreduce_probe([0], min_bytes=1 << 10, max_bytes=1 << 22, warmup=1, iters=3)
+    assert [r.bytes for r in rows] == [1 << k for k in range(10, 23)]
+    assert all(r.mismatches == 0 and r.nccl_result == 0 and r.best_ms > 0 for r in rows)
+    assert all(r.busbw_gbs == 0.0 for r in rows)            # 2(n-1)/n = 0 at n = 1
+
+
+def test_allreduce_probe_all_devices(capi, gpu):
+    if gpu < 2:
+        pytest.skip("needs at least two GPUs")
+    rows = capi.allreduce_probe(list(range(gpu)), min_bytes=1 << 10, max_bytes=1 << 26, warmup=2, iters=5)
+    assert len(rows) == 17
+    assert all(r.mismatches == 0 and r.nccl_result == 0 for r in rows)   # bit-exact vs closed form
+    top = rows[-1]
+    assert abs(top.busbw_gbs - top.algbw_gbs * 2 * (gpu - 1) / gpu) < 1e-6
+    assert top.busbw_gbs > 50.0
+
+
+def _run_bin(name, tmp_path, **env):
+    exe = os.path.join(ROOT, "nvidia-gpu-operator-k8s-cluster_b200", "bin", name)
+    e = dict(os.environ, OUTPUT_DIR=str(tmp_path))
+    e.update({k: str(v) for k, v in env.items()})
+    p = subprocess.run([exe], env=e, capture_output=True, text=True, timeout=600)
+    return p.returncode, p.stdout, p.stderr
+
+
+def test_vectoradd_executable_on_gpu(gpu, tmp_path):
+    rc, out, err = _run_bin("vectorAdd", tmp_path)
+    assert rc == 0, err
+    lines = out.splitlines()
+    assert lines[0] == "[Vector addition of 50000 elements]" and lines[-2:] == ["Test PASSED", "Done"]
+    assert "CUDA kernel launch with 7 blocks of 1024 threads" in lines
+
+
+def test_validator_executable_fanout_on_gpu(gpu, tmp_path):
+    """The drop-in entrypoint as kubelet runs it: every visible GPU validated, status files
+    written; then a corrupted element makes it exit 1 and leave no cuda-ready."""
+    rc, out, err = _run_bin("nvidia-validator", tmp_path, COMPONENT="cuda")
+    assert rc == 0, err
+    want = ["cuda-gpu%d-ready" % i for i in range(gpu)] + ["cuda-ready"]
+    assert sorted(f for f in os.listdir(tmp_path)) == sorted(want)
+    assert out.count("Test PASSED") == gpu
+    rc, out, err = _run_bin("nvidia-validator", tmp_path, COMPONENT="cuda", B200V_INJECT_FAULT=31337)
+    assert rc == 1 and "Result verification failed at element 31337!" in err
+    assert "cuda-ready" not in os.listdir(tmp_path)
+    rc, out, err = _run_bin("nvidia-validator", tmp_path, COMPONENT="cuda", B200V_ELEMS=(1 << 24) + 3)
+    assert rc == 0 and "cuda-ready" in os.listdir(tmp_path)
