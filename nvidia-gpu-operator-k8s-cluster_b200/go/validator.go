@@ -24,6 +24,7 @@ import (
 	"flag"
 	"fmt"
 	"math"
+	"net/http"
 	"os"
 	"os/exec"
 	"path/filepath"
@@ -290,6 +291,107 @@ func validateToolkit(c *config) int {
 	return validateWithSmi(c, "toolkit-ready", "toolkit", []string{c.nvidiaSmi})
 }
 
+// readAllocatableGPUs mirrors read_allocatable_gpus: B200V_ALLOCATABLE_GPUS, else the first
+// integer after "nvidia.com/gpu" (or a bare number) in B200V_ALLOCATABLE_FILE; -1 = no source.
+func readAllocatableGPUs() int64 {
+	if v := os.Getenv("B200V_ALLOCATABLE_GPUS"); v != "" {
+		n, err := strconv.ParseInt(v, 10, 64)
+		if err != nil || n < 0 {
+			return 0
+		}
+		return n
+	}
+	path := os.Getenv("B200V_ALLOCATABLE_FILE")
+	if path == "" {
+		return -1
+	}
+	raw, err := os.ReadFile(path)
+	if err != nil {
+		return 0
+	}
+	text := strings.TrimSpace(string(raw))
+	if n, err := strconv.ParseInt(text, 10, 64); err == nil && n >= 0 {
+		return n
+	}
+	at := strings.Index(text, "nvidia.com/gpu")
+	if at < 0 {
+		return 0
+	}
+	rest := strings.TrimLeft(text[at+len("nvidia.com/gpu"):], ":\"'= \t")
+	end := 0
+	for end < len(rest) && rest[end] >= '0' && rest[end] <= '9' {
+		end++
+	}
+	n, err := strconv.ParseInt(rest[:end], 10, 64)
+	if err != nil {
+		return 0
+	}
+	return n
+}
+
+// validatePlugin mirrors validate_plugin (SURVEY.md §8f-1).
+func validatePlugin(c *config) int {
+	if err := deleteStatusFile(c, "plugin-ready"); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to remove stale plugin-ready: %v\n", err)
+		return 1
+	}
+	gpus := readAllocatableGPUs()
+	if gpus == -1 {
+		fmt.Fprintln(os.Stderr, "plugin validation needs the node's allocatable nvidia.com/gpu count: set "+
+			"B200V_ALLOCATABLE_GPUS or B200V_ALLOCATABLE_FILE (no Kubernetes client in this build)")
+		return 1
+	}
+	retries := envInt("B200V_PLUGIN_RETRIES", 30)
+	for attempt := 1; gpus <= 0 && attempt < retries; attempt++ {
+		fmt.Fprintf(os.Stderr, "GPU resources are not yet discovered by the node, retry: %d\n", attempt)
+		time.Sleep(time.Duration(c.sleepSeconds) * time.Second)
+		gpus = readAllocatableGPUs()
+	}
+	if gpus <= 0 {
+		fmt.Fprintln(os.Stderr, "GPU resources are not discovered by the node")
+		return 1
+	}
+	fmt.Printf("node advertises nvidia.com/gpu: %d\n", gpus)
+	if c.withWorkload && runVectorAddSample(0, c.elems, c.injectFault) != 0 {
+		return 1
+	}
+	if err := createStatusFile(c, "plugin-ready"); err != nil {
+		fmt.Fprintf(os.Stderr, "unable to create status file plugin-ready: %v\n", err)
+		return 1
+	}
+	fmt.Println("plugin validation is successful")
+	return 0
+}
+
+// renderMetrics mirrors render_metrics (SURVEY.md §8f-2): status-file gauges plus *.prom files.
+func renderMetrics(c *config) string {
+	var b strings.Builder
+	for _, comp := range []string{"driver", "toolkit", "cuda", "plugin"} {
+		name := "gpu_operator_node_" + comp + "_ready"
+		v := 0
+		if _, err := os.Stat(statusPath(c, comp+"-ready")); err == nil {
+			v = 1
+		}
+		fmt.Fprintf(&b, "# HELP %s 1 when %s validation has left its status file on this node\n# TYPE %s gauge\n%s %d\n",
+			name, comp, name, name, v)
+	}
+	perGPU, _ := filepath.Glob(statusPath(c, "cuda-gpu*-ready"))
+	b.WriteString("# HELP b200v_node_cuda_gpu_ready 1 for every GPU whose own vectorAdd validation passed\n# TYPE b200v_node_cuda_gpu_ready gauge\n")
+	for _, f := range perGPU {
+		idx := strings.TrimSuffix(strings.TrimPrefix(filepath.Base(f), "cuda-gpu"), "-ready")
+		fmt.Fprintf(&b, "b200v_node_cuda_gpu_ready{gpu=\"%s\"} 1\n", idx)
+	}
+	fmt.Fprintf(&b, "# HELP gpu_operator_node_device_plugin_devices_total GPUs that passed cuda validation on this node\n"+
+		"# TYPE gpu_operator_node_device_plugin_devices_total gauge\ngpu_operator_node_device_plugin_devices_total %d\n", len(perGPU))
+	proms, _ := filepath.Glob(statusPath(c, "*.prom"))
+	for _, f := range proms {
+		if raw, err := os.ReadFile(f); err == nil {
+			b.Write(raw)
+		}
+	}
+	return b.String()
+}
+
 func runStreamSweep(c *config) int {
 	ops := []struct {
 		id   C.int
@@ -372,6 +474,14 @@ func main() {
 		fmt.Fprintln(os.Stderr, "invalid -c <component-name> flag: must not be empty string")
 		os.Exit(1)
 	}
+	if c.component == "metrics" { // node-status-exporter mode: serve /metrics on METRICS_PORT
+		http.HandleFunc("/metrics", func(w http.ResponseWriter, _ *http.Request) {
+			w.Header().Set("Content-Type", "text/plain; version=0.0.4")
+			fmt.Fprint(w, renderMetrics(c))
+		})
+		fmt.Fprintln(os.Stderr, http.ListenAndServe(":"+envOr("METRICS_PORT", "8000"), nil))
+		os.Exit(1)
+	}
 	if c.childDevice >= 0 {
 		os.Exit(runVectorAddSample(c.childDevice, c.elems, c.injectFault))
 	}
@@ -384,6 +494,8 @@ func main() {
 			rc = validateDriver(c)
 		case "toolkit":
 			rc = validateToolkit(c)
+		case "plugin":
+			rc = validatePlugin(c)
 		}
 		if rc == -1 {
 			fmt.Fprintf(os.Stderr, "invalid component specified for validation: %s (this build supports cuda, driver, toolkit)\n", c.component)

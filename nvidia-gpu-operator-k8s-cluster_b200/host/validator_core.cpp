@@ -2,6 +2,8 @@
 // reached only through the Api table (the C ABI of include/b200validate.h).
 #include "validator_core.h"
 
+#include <algorithm>
+#include <arpa/inet.h>
 #include <cerrno>
 #include <cinttypes>
 #include <cmath>
@@ -9,6 +11,8 @@
 #include <cstring>
 #include <dirent.h>
 #include <fcntl.h>
+#include <netinet/in.h>
+#include <sys/socket.h>
 #include <sys/stat.h>
 #include <sys/types.h>
 #include <sys/wait.h>
@@ -80,6 +84,11 @@ bool parse_config(int argc, char **argv, Config &cfg) {
     long long inj;
     if (parse_ll(env_or("B200V_INJECT_FAULT", ""), inj)) cfg.inject_fault = inj;
     cfg.child_device = env_int("B200V_CHILD_DEVICE", -1);
+    cfg.allocatable_gpus = env_or("B200V_ALLOCATABLE_GPUS", "");
+    cfg.allocatable_file = env_or("B200V_ALLOCATABLE_FILE", "");
+    cfg.plugin_retries = env_int("B200V_PLUGIN_RETRIES", 30);
+    cfg.metrics_port = env_int("METRICS_PORT", 8000);
+    cfg.write_prom = parse_bool(env_or("B200V_WRITE_PROM", ""), false);
     cfg.nvidia_smi = env_or("B200V_NVIDIA_SMI", "nvidia-smi");
     cfg.driver_root = env_or("DRIVER_ROOT", "/run/nvidia/driver");
     char self[4096];
@@ -113,6 +122,12 @@ bool parse_config(int argc, char **argv, Config &cfg) {
         else if (a == "--node-name") { if (!need(cfg.node_name)) return false; }
         else if (a == "--namespace" || a == "-n") { if (!need(cfg.operator_namespace)) return false; }
         else if (a == "--mode") { if (!need(cfg.mode)) return false; }
+        else if (a == "--metrics-port" || a == "-p") {
+            if (!need(tmp)) return false;
+            long long port;
+            if (!parse_ll(tmp, port) || port < 0 || port > 65535) { cfg.error = "bad --metrics-port: " + tmp; return false; }
+            cfg.metrics_port = (int)port;
+        }
         else if (a == "--elems") {
             if (!need(tmp)) return false;
             if (!parse_size(tmp, cfg.elems)) { cfg.error = "bad --elems: " + tmp; return false; }
@@ -348,6 +363,196 @@ int validate_toolkit(const Config &cfg, FILE *out, FILE *err) {
     return validate_with_smi(cfg, "toolkit-ready", cfg.nvidia_smi, "toolkit", out, err);
 }
 
+// ---- COMPONENT=plugin --------------------------------------------------------------------------------------
+
+namespace {
+// First integer that follows `key` in `text` (skipping separators and quotes), or -1.
+long long number_after(const std::string &text, const std::string &key) {
+    size_t at = text.find(key);
+    if (at == std::string::npos) return -1;
+    at += key.size();
+    while (at < text.size() && (text[at] == ':' || text[at] == '"' || text[at] == '\'' || text[at] == ' ' ||
+                                text[at] == '\t' || text[at] == '='))
+        ++at;
+    size_t end = at;
+    while (end < text.size() && text[end] >= '0' && text[end] <= '9') ++end;
+    long long v;
+    return (end > at && parse_ll(text.substr(at, end - at), v)) ? v : -1;
+}
+
+std::string read_file(const std::string &path, bool &ok) {
+    std::string s;
+    FILE *f = std::fopen(path.c_str(), "rb");
+    ok = f != nullptr;
+    if (!f) return s;
+    char buf[4096];
+    size_t got;
+    while ((got = std::fread(buf, 1, sizeof buf, f)) > 0) s.append(buf, got);
+    std::fclose(f);
+    return s;
+}
+}  // namespace
+
+long long read_allocatable_gpus(const Config &cfg) {
+    long long v;
+    if (!cfg.allocatable_gpus.empty()) return parse_ll(cfg.allocatable_gpus, v) && v >= 0 ? v : 0;
+    if (cfg.allocatable_file.empty()) return -1;
+    bool ok = false;
+    std::string text = read_file(cfg.allocatable_file, ok);
+    if (!ok) return 0;                                   // not written yet: nothing advertised so far
+    while (!text.empty() && (text.back() == '\n' || text.back() == ' ' || text.back() == '\r')) text.pop_back();
+    if (parse_ll(text, v)) return v >= 0 ? v : 0;        // a bare number
+    v = number_after(text, "nvidia.com/gpu");            // `nvidia.com/gpu: 8`, JSON or describe output
+    return v >= 0 ? v : 0;
+}
+
+int validate_plugin(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    if (!delete_status_file(cfg, "plugin-ready")) {
+        std::fprintf(err, "unable to remove stale plugin-ready: %s\n", std::strerror(errno));
+        return 1;
+    }
+    long long gpus = read_allocatable_gpus(cfg);
+    if (gpus == -1) {
+        std::fprintf(err, "plugin validation needs the node's allocatable nvidia.com/gpu count: set "
+                          "B200V_ALLOCATABLE_GPUS or B200V_ALLOCATABLE_FILE (no Kubernetes client in this build)\n");
+        return 1;
+    }
+    for (int attempt = 1; gpus <= 0 && attempt < cfg.plugin_retries; ++attempt) {
+        std::fprintf(err, "GPU resources are not yet discovered by the node, retry: %d\n", attempt);
+        std::fflush(nullptr);
+        ::sleep((unsigned)cfg.sleep_seconds);
+        gpus = read_allocatable_gpus(cfg);
+    }
+    if (gpus <= 0) {
+        std::fprintf(err, "GPU resources are not discovered by the node\n");
+        return 1;
+    }
+    std::fprintf(out, "node advertises nvidia.com/gpu: %lld\n", gpus);
+    if (cfg.with_workload) {
+        // Upstream runs the workload in a pod limited to nvidia.com/gpu: 1; here the container's
+        // own first device (what the device plugin granted it) runs it in-process.
+        if (run_vectoradd_sample(api, 0, cfg.elems, cfg.inject_fault, out, err) != 0) return 1;
+    }
+    if (!create_status_file(cfg, "plugin-ready")) {
+        std::fprintf(err, "unable to create status file plugin-ready: %s\n", std::strerror(errno));
+        return 1;
+    }
+    std::fprintf(out, "plugin validation is successful\n");
+    return 0;
+}
+
+// ---- COMPONENT=metrics ---------------------------------------------------------------------------------------
+
+std::string render_metrics(const Config &cfg) {
+    std::string m;
+    struct stat st;
+    const char *components[] = {"driver", "toolkit", "cuda", "plugin"};
+    for (const char *c : components) {
+        const std::string name = std::string("gpu_operator_node_") + c + "_ready";
+        const bool ready = ::stat(status_path(cfg, std::string(c) + "-ready").c_str(), &st) == 0;
+        m += "# HELP " + name + " 1 when " + c + " validation has left its status file on this node\n";
+        m += "# TYPE " + name + " gauge\n";
+        m += name + (ready ? " 1\n" : " 0\n");
+    }
+    // per-GPU fan-out files and bandwidth results
+    std::vector<std::string> gpu_lines, prom_files;
+    if (DIR *d = ::opendir(cfg.output_dir.c_str())) {
+        while (dirent *e = ::readdir(d)) {
+            const std::string f = e->d_name;
+            if (f.rfind("cuda-gpu", 0) == 0 && ends_with(f, "-ready")) {
+                const std::string idx = f.substr(8, f.size() - 8 - 6);
+                gpu_lines.push_back("b200v_node_cuda_gpu_ready{gpu=\"" + idx + "\"} 1\n");
+            } else if (ends_with(f, ".prom")) {
+                prom_files.push_back(f);
+            }
+        }
+        ::closedir(d);
+    }
+    std::sort(gpu_lines.begin(), gpu_lines.end());
+    std::sort(prom_files.begin(), prom_files.end());
+    m += "# HELP b200v_node_cuda_gpu_ready 1 for every GPU whose own vectorAdd validation passed\n";
+    m += "# TYPE b200v_node_cuda_gpu_ready gauge\n";
+    for (const std::string &l : gpu_lines) m += l;
+    m += "# HELP gpu_operator_node_device_plugin_devices_total GPUs that passed cuda validation on this node\n";
+    m += "# TYPE gpu_operator_node_device_plugin_devices_total gauge\n";
+    m += "gpu_operator_node_device_plugin_devices_total " + std::to_string(gpu_lines.size()) + "\n";
+    for (const std::string &f : prom_files) {
+        bool ok = false;
+        const std::string text = read_file(status_path(cfg, f), ok);
+        if (ok) m += text;
+        if (ok && !text.empty() && text.back() != '\n') m += "\n";
+    }
+    return m;
+}
+
+int serve_metrics(const Config &cfg, FILE *out, FILE *err) {
+    if (parse_bool(env_or("B200V_METRICS_ONESHOT", ""), false)) {
+        const std::string m = render_metrics(cfg);
+        std::fwrite(m.data(), 1, m.size(), out);
+        std::fflush(out);
+        return 0;
+    }
+    const int max_requests = env_int("B200V_METRICS_MAX_REQUESTS", 0);   // 0 = serve forever
+    int srv = ::socket(AF_INET, SOCK_STREAM, 0);
+    if (srv < 0) {
+        std::fprintf(err, "metrics: socket: %s\n", std::strerror(errno));
+        return 1;
+    }
+    int one = 1;
+    ::setsockopt(srv, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+    sockaddr_in addr;
+    std::memset(&addr, 0, sizeof addr);
+    addr.sin_family = AF_INET;
+    addr.sin_addr.s_addr = htonl(INADDR_ANY);
+    addr.sin_port = htons((uint16_t)cfg.metrics_port);
+    if (::bind(srv, (sockaddr *)&addr, sizeof addr) != 0 || ::listen(srv, 16) != 0) {
+        std::fprintf(err, "metrics: cannot listen on port %d: %s\n", cfg.metrics_port, std::strerror(errno));
+        ::close(srv);
+        return 1;
+    }
+    socklen_t alen = sizeof addr;
+    ::getsockname(srv, (sockaddr *)&addr, &alen);
+    std::fprintf(out, "metrics: listening on :%d/metrics\n", (int)ntohs(addr.sin_port));
+    std::fflush(out);
+    for (int served = 0; max_requests == 0 || served < max_requests; ++served) {
+        int c = ::accept(srv, nullptr, nullptr);
+        if (c < 0) {
+            if (errno == EINTR) { --served; continue; }
+            break;
+        }
+        char req[2048];
+        ssize_t got = ::recv(c, req, sizeof req - 1, 0);
+        req[got > 0 ? got : 0] = 0;
+        const bool is_metrics = std::strncmp(req, "GET /metrics", 12) == 0 || std::strncmp(req, "GET / ", 6) == 0;
+        const std::string body = is_metrics ? render_metrics(cfg) : std::string("not found\n");
+        std::string resp = std::string(is_metrics ? "HTTP/1.1 200 OK\r\n" : "HTTP/1.1 404 Not Found\r\n") +
+                           "Content-Type: text/plain; version=0.0.4\r\nConnection: close\r\nContent-Length: " +
+                           std::to_string(body.size()) + "\r\n\r\n" + body;
+        size_t off = 0;
+        while (off < resp.size()) {
+            ssize_t w = ::send(c, resp.data() + off, resp.size() - off, MSG_NOSIGNAL);
+            if (w <= 0) break;
+            off += (size_t)w;
+        }
+        ::close(c);
+    }
+    ::close(srv);
+    return 0;
+}
+
+namespace {
+// Textfile-collector style result files the metrics mode re-exports.
+void write_prom(const Config &cfg, const std::string &file, const std::string &text) {
+    if (!cfg.write_prom) return;
+    const std::string tmp = status_path(cfg, file + ".tmp"), dst = status_path(cfg, file);
+    if (FILE *f = std::fopen(tmp.c_str(), "wb")) {
+        std::fwrite(text.data(), 1, text.size(), f);
+        std::fclose(f);
+        std::rename(tmp.c_str(), dst.c_str());
+    }
+}
+}  // namespace
+
 // ---- sweeps -------------------------------------------------------------------------------------------
 
 int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
@@ -365,6 +570,8 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     api.device_info(dev, &info);
     const double nominal = 2.0 * info.mem_clock_khz * 1e3 * info.mem_bus_bits / 8.0 / 1e9;
     int failures = 0;
+    std::string prom = "# HELP b200v_hbm_bandwidth_gbs median GB/s of the STREAM op on HBM-bound sizes\n"
+                       "# TYPE b200v_hbm_bandwidth_gbs gauge\n";
     for (int lg = lo; lg <= hi; ++lg) {
         const size_t n = (size_t)1 << lg;
         for (int op : ops) {
@@ -385,8 +592,15 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
                          r.l2_resident, nominal > 0 ? r.median_gbs / nominal : 0.0, nominal, r.grid, r.block,
                          r.mismatches, r.digest);
             std::fflush(out);
+            if (!r.l2_resident && !r.mismatches) {
+                char line[256];
+                std::snprintf(line, sizeof line, "b200v_hbm_bandwidth_gbs{gpu=\"%d\",op=\"%s\",log2_n=\"%d\"} %.1f\n",
+                              dev, kOpNames[op], lg, r.median_gbs);
+                prom += line;
+            }
         }
     }
+    write_prom(cfg, "hbm-bandwidth.prom", prom);
     return failures ? 1 : 0;
 }
 
@@ -421,9 +635,15 @@ int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     int failures = rc != B200V_OK ? 1 : 0;
     if (rc != B200V_OK) std::fprintf(err, "nccl probe failed: %s\n", api.strerror(rc));
     const double min_busbw = std::atof(env_or("B200V_MIN_BUSBW_GBS", "0").c_str());
+    std::string prom = "# HELP b200v_nvlink_allreduce_busbw_gbs NCCL all-reduce bus bandwidth, GB/s\n"
+                       "# TYPE b200v_nvlink_allreduce_busbw_gbs gauge\n";
     for (int i = 0; i < nrows; ++i) {
         const b200v_ar_row &r = rows[(size_t)i];
         if (r.mismatches) ++failures;
+        char line[256];
+        std::snprintf(line, sizeof line, "b200v_nvlink_allreduce_busbw_gbs{ranks=\"%d\",bytes=\"%" PRIu64 "\"} %.2f\n",
+                      use, r.bytes, r.busbw_gbs);
+        prom += line;
         std::fprintf(out,
                      "{\"mode\":\"nccl\",\"ranks\":%d,\"bytes\":%" PRIu64 ",\"best_ms\":%.5f,\"median_ms\":%.5f,"
                      "\"algbw_gbs\":%.2f,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%" PRIu64 "}\n",
@@ -436,6 +656,7 @@ int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
         ++failures;
     }
     std::fflush(out);
+    if (!failures) write_prom(cfg, "nvlink-busbw.prom", prom);
     return failures ? 1 : 0;
 }
 
@@ -453,6 +674,7 @@ int validator_main(const Api &api, int argc, char **argv) {
         std::fprintf(stderr, "invalid -c <component-name> flag: must not be empty string\n");
         return 1;
     }
+    if (cfg.component == "metrics") return serve_metrics(cfg, stdout, stderr);
     if (cfg.child_device >= 0) {   // fan-out child: validate exactly one device, no status files
         const long long inj = (env_int("B200V_INJECT_DEVICE", -1) < 0 ||
                                env_int("B200V_INJECT_DEVICE", -1) == cfg.child_device) ? cfg.inject_fault : -1;
@@ -462,16 +684,17 @@ int validator_main(const Api &api, int argc, char **argv) {
         if (cfg.component == "cuda") return validate_cuda(api, cfg, stdout, stderr);
         if (cfg.component == "driver") return validate_driver(cfg, stdout, stderr);
         if (cfg.component == "toolkit") return validate_toolkit(cfg, stdout, stderr);
+        if (cfg.component == "plugin") return validate_plugin(api, cfg, stdout, stderr);
         return -1;
     };
     int tries = 0;
     for (;;) {
         int rc = once();
         if (rc == -1) {
-            // plugin, mofed, vfio-pci, vgpu-manager, vgpu-devices, cc-manager, nvidia-fs and metrics
-            // belong to other parts of the operator; this image covers the GPU workload path only.
+            // mofed, vfio-pci, vgpu-manager, vgpu-devices, cc-manager and nvidia-fs belong to other
+            // parts of the operator; this image covers the GPU workload path only.
             std::fprintf(stderr, "invalid component specified for validation: %s (this build supports cuda, "
-                                 "driver, toolkit)\n", cfg.component.c_str());
+                                 "driver, toolkit, plugin, metrics)\n", cfg.component.c_str());
             return 1;
         }
         if (rc == 0) return 0;

@@ -53,6 +53,11 @@ struct Config {
     int max_retries = 0;                         // B200V_MAX_RETRIES: 0 = forever (upstream)
     long long inject_fault = -1;                 // B200V_INJECT_FAULT: corrupt this output element
     int child_device = -1;                       // B200V_CHILD_DEVICE: set by the fan-out parent
+    std::string allocatable_gpus;                // B200V_ALLOCATABLE_GPUS: node allocatable nvidia.com/gpu
+    std::string allocatable_file;                // B200V_ALLOCATABLE_FILE: file holding that count
+    int plugin_retries = 30;                     // B200V_PLUGIN_RETRIES (upstream: 30 x 5 s)
+    int metrics_port = 8000;                     // METRICS_PORT / --metrics-port (upstream default)
+    bool write_prom = false;                     // B200V_WRITE_PROM: sweeps leave *.prom files
     std::string nvidia_smi = "nvidia-smi";       // B200V_NVIDIA_SMI: command for driver/toolkit
     std::string driver_root = "/run/nvidia/driver";
     std::string self_exe;                        // path re-executed for fan-out children
@@ -80,6 +85,20 @@ long long verify_result(const float *A, const float *B, const float *C, size_t n
 int validate_cuda(const Api &api, const Config &cfg, FILE *out, FILE *err);
 int validate_driver(const Config &cfg, FILE *out, FILE *err);
 int validate_toolkit(const Config &cfg, FILE *out, FILE *err);
+
+// COMPONENT=plugin: wait until the node advertises nvidia.com/gpu (the field the
+// runbook greps at reference README.md:122), then run the workload and create plugin-ready.  This
+// build has no Kubernetes client, so the allocatable count comes from B200V_ALLOCATABLE_GPUS or
+// from B200V_ALLOCATABLE_FILE (a bare number, or text containing `nvidia.com/gpu: N` as printed
+// by `kubectl describe node` / a downward-API-fed sidecar).  -1 = no source configured.
+long long read_allocatable_gpus(const Config &cfg);
+int validate_plugin(const Api &api, const Config &cfg, FILE *out, FILE *err);
+
+// COMPONENT=metrics: node-status-exporter compatible gauges from the status
+// files (nodeStatusExporter.enabled=true at reference README.md:107), plus every *.prom file the
+// sweeps left in OUTPUT_DIR, so HBM and NVLink bandwidth become node health signals.
+std::string render_metrics(const Config &cfg);
+int serve_metrics(const Config &cfg, FILE *out, FILE *err);
 
 // B200V_MODE=stream / nccl: the bandwidth sweeps, one JSON line per row on `out`.
 int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err);

@@ -131,7 +131,7 @@ def test_flags_override_environment(fake, tmp_path):
 def test_component_validation(fake, tmp_path):
     rc, _out, err = run(fake, tmp_path)
     assert rc == 1 and "must not be empty string" in err
-    for comp in ("plugin", "mofed", "metrics", "nope"):
+    for comp in ("mofed", "vfio-pci", "nvidia-fs", "nope"):
         rc, _out, err = run(fake, tmp_path, COMPONENT=comp)
         assert rc == 1 and "invalid component specified for validation: %s" % comp in err
     assert ready(tmp_path) == []
@@ -181,3 +181,75 @@ def test_stream_and_nccl_modes_emit_json_rows(fake, tmp_path):
     assert rc == 1 and "below the required 720.0 GB/s" in err
     rc, _out, _err = run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=2, FAKE_MODE="wrong", B200V_MAX_LOG2=12)
     assert rc == 1
+
+
+# ---- plugin component and node-status-exporter metrics -----------------
+
+def test_plugin_waits_for_allocatable_then_validates(fake, tmp_path):
+    alloc = tmp_path / "allocatable"
+    rc, out, err = run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=8)
+    assert rc == 0, err
+    assert "node advertises nvidia.com/gpu: 8" in out and "Test PASSED" in out
+    assert ready(tmp_path) == ["plugin-ready"]
+    # the field as `kubectl describe node` prints it (what README.md:122 greps for)
+    alloc.write_text("Allocatable:\n  cpu: 192\n  nvidia.com/gpu:     8\n  pods: 110\n")
+    rc, out, _err = run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_FILE=alloc, WITH_WORKLOAD="false")
+    assert rc == 0 and "nvidia.com/gpu: 8" in out and "Test PASSED" not in out
+    alloc.write_text('{"status": {"allocatable": {"nvidia.com/gpu": "4"}}}')
+    rc, out, _err = run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_FILE=alloc)
+    assert rc == 0 and "nvidia.com/gpu: 4" in out
+
+
+def test_plugin_fails_when_no_gpu_is_advertised(fake, tmp_path):
+    (tmp_path / "plugin-ready").write_text("")
+    rc, _out, err = run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=0, B200V_PLUGIN_RETRIES=3)
+    assert rc == 1
+    assert err.count("GPU resources are not yet discovered by the node, retry") == 2
+    assert "GPU resources are not discovered by the node" in err
+    assert ready(tmp_path) == []
+    rc, _out, err = run(fake, tmp_path, COMPONENT="plugin")
+    assert rc == 1 and "no Kubernetes client in this build" in err
+    rc, _out, err = run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=1, FAKE_MODE="wrong")
+    assert rc == 1 and "Result verification failed" in err and ready(tmp_path) == []
+
+
+def test_metrics_oneshot_reflects_status_files_and_bandwidth(fake, tmp_path):
+    run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=2)
+    run(fake, tmp_path, COMPONENT="toolkit", B200V_NVIDIA_SMI="true")
+    run(fake, tmp_path, B200V_MODE="stream", B200V_MIN_LOG2=27, B200V_MAX_LOG2=28, B200V_WRITE_PROM=1)
+    run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=8, B200V_MAX_LOG2=11, B200V_WRITE_PROM=1)
+    rc, out, _err = run(fake, tmp_path, COMPONENT="metrics", B200V_METRICS_ONESHOT=1)
+    assert rc == 0
+    lines = out.splitlines()
+    assert "gpu_operator_node_cuda_ready 1" in lines and "gpu_operator_node_toolkit_ready 1" in lines
+    assert "gpu_operator_node_driver_ready 0" in lines and "gpu_operator_node_plugin_ready 0" in lines
+    assert 'b200v_node_cuda_gpu_ready{gpu="0"} 1' in lines and 'b200v_node_cuda_gpu_ready{gpu="1"} 1' in lines
+    assert "gpu_operator_node_device_plugin_devices_total 2" in lines
+    assert any(l.startswith('b200v_hbm_bandwidth_gbs{gpu="0",op="triad",log2_n="28"} ') for l in lines)
+    assert 'b200v_nvlink_allreduce_busbw_gbs{ranks="8",bytes="2048"} 700.00' in lines
+    # every sample line is `name{labels} value` or `name value`, every family has HELP and TYPE
+    for l in lines:
+        assert l.startswith("#") or len(l.rsplit(" ", 1)) == 2
+    assert out.count("# TYPE") >= 7
+
+
+def test_metrics_http_endpoint(fake, tmp_path):
+    import socket
+    import urllib.request
+    (tmp_path / "driver-ready").write_text("")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = {"PATH": os.environ["PATH"], "OUTPUT_DIR": str(tmp_path), "COMPONENT": "metrics",
+           "B200V_METRICS_MAX_REQUESTS": "2"}
+    p = subprocess.Popen([fake, "--metrics-port", str(port)], env=env, stdout=subprocess.PIPE, text=True)
+    try:
+        assert "listening on :%d/metrics" % port in p.stdout.readline()
+        body = urllib.request.urlopen("http://127.0.0.1:%d/metrics" % port, timeout=10).read().decode()
+        assert "gpu_operator_node_driver_ready 1" in body and "gpu_operator_node_cuda_ready 0" in body
+        with pytest.raises(Exception):
+            urllib.request.urlopen("http://127.0.0.1:%d/other" % port, timeout=10)
+        assert p.wait(timeout=10) == 0
+    finally:
+        if p.poll() is None:
+            p.kill()
