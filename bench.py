@@ -191,6 +191,13 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly one JSON line.  Libraries underneath (NCCL prints a version banner when
+    # a communicator is created) write to fd 1 directly, so fd 1 points at stderr for the whole run
+    # and the result goes to the saved descriptor at the end.
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import numpy as np  # noqa: F401
     import torch
     import torch.distributed as dist
@@ -339,6 +346,28 @@ def main():
                      "busbw_gbs_at_1GiB": top["busbw_gbs"], "frac_of_900": round(top["busbw_gbs"] / 900.0, 4),
                      "bit_exact": all(t["mismatches"] == 0 for t in table), "rows": table}
 
+    # ---- hand-written NVLink-multicast all-reduce (single process drives all GPUs) ---------------
+    # Rank 0 runs it over every GPU of the job while the other ranks wait on the HOST (a gloo
+    # barrier): they must not wait inside a GPU kernel, which would share the GPUs with the probe.
+    nvls = None
+    if world > 1 and not args.no_allreduce:
+        torch.cuda.synchronize()
+        host_group = dist.new_group(backend="gloo")
+        dist.barrier(group=host_group)
+        if rank == 0:
+            try:
+                vrows = capi.nvls_allreduce_probe(list(range(world)), min_bytes=1 << 20, max_bytes=1 << 30,
+                                                  warmup=5, iters=20)
+                vt = [{"bytes": int(r.bytes), "ms": round(r.best_ms, 4), "algbw_gbs": round(r.algbw_gbs, 1),
+                       "busbw_gbs": round(r.busbw_gbs, 1), "mismatches": int(r.mismatches)} for r in vrows]
+                nvls = {"op": "multimem.ld_reduce + multimem.st kernel, fp32 sum in place, one process",
+                        "busbw_gbs_at_1GiB": vt[-1]["busbw_gbs"], "frac_of_900": round(vt[-1]["busbw_gbs"] / 900.0, 4),
+                        "bit_exact": all(t["mismatches"] == 0 for t in vt), "gpu_launches": world * len(vt) * 26,
+                        "rows": vt}
+            except capi.B200VError as e:
+                nvls = {"unavailable": str(e)}
+        dist.barrier(group=host_group)
+
     # ---- CPU baseline: the sample's host verification loop, one thread, rank 0 at N=1 -------------
     cpu = None
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
@@ -373,7 +402,10 @@ def main():
             line["cpu_baseline"] = cpu
         if allreduce:
             line["allreduce"] = allreduce
-        print(json.dumps(line))
+        if nvls:
+            line["nvls_allreduce"] = nvls
+        sys.stdout.flush()
+        os.write(result_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
     return 0

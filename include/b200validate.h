@@ -42,6 +42,9 @@ extern "C" {
 #define B200V_E_NONCCL     (-5)  /* libnccl.so.2 could not be loaded */
 #define B200V_E_NOMEM      (-6)  /* host allocation failed */
 #define B200V_E_TOOLARGE   (-7)  /* n exceeds the fixed capacity of a no-allocation entry point */
+#define B200V_E_UNSUPPORTED (-8) /* the devices or the driver lack a required feature (e.g. multicast) */
+#define B200V_E_DRIVER     (-9)  /* a CUDA driver API call failed; CUresult in b200v_last_driver_error */
+#define B200V_E_TIMEOUT    (-10) /* a cross-GPU barrier did not complete in time */
 
 /* Elementwise ops.  dst = f(x, y, s), fp32, round-to-nearest-even, denormals kept (no -ftz):
  *   COPY dst=x   SCALE dst=s*x   ADD dst=x+y   TRIAD dst=fmaf(s,y,x) (one FFMA)
@@ -211,6 +214,16 @@ int b200v_allreduce_probe_rank(int dev, int rank, int nranks,
                                b200v_ar_row *rows, int max_rows, int *nrows);
 int b200v_nccl_version(int *version);
 int b200v_last_nccl_error(void);
+
+/* A second, hand-written NVLink probe (nothing upstream): the same sweep, input
+ * pattern, bit-exact check and row format as b200v_allreduce_probe, but the all-reduce is one
+ * sm_100a kernel per GPU that reduces inside the NVSwitch (multimem.ld_reduce) and broadcasts
+ * through it (multimem.st) over a CUDA multicast object.  Single process, 2 <= ndev, sizes are
+ * multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast
+ * support, B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
+int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
+                               int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
+int b200v_last_driver_error(void);
 
 /* Releases cached per-device state (streams, events, staging buffers). */
 int b200v_shutdown(void);

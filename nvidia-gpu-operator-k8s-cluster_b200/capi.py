@@ -83,6 +83,8 @@ SIGNATURES = {
     "b200v_allreduce_probe_rank": (_i, [_i, _i, _i, ctypes.c_char_p, _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_nccl_version": (_i, [_P(_i)]),
     "b200v_last_nccl_error": (_i, []),
+    "b200v_nvls_allreduce_probe": (_i, [_i, _P(_i), _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
+    "b200v_last_driver_error": (_i, []),
     "b200v_shutdown": (_i, []),
 }
 
@@ -262,6 +264,20 @@ def allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20)
     n = _i()
     _check(lib().b200v_allreduce_probe(len(devs), arr, min_bytes, max_bytes, warmup, iters, rows, 64,
                                        ctypes.byref(n)), "b200v_allreduce_probe")
+    return _rows(rows, n.value)
+
+
+E_UNSUPPORTED, E_DRIVER, E_TIMEOUT = -8, -9, -10
+
+
+def nvls_allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20):
+    """The hand-written NVLink-multicast all-reduce probe; same rows as allreduce_probe."""
+    devs = list(devs)
+    arr = (_i * len(devs))(*devs)
+    rows = (ArRow * 64)()
+    n = _i()
+    _check(lib().b200v_nvls_allreduce_probe(len(devs), arr, min_bytes, max_bytes, warmup, iters, rows, 64,
+                                            ctypes.byref(n)), "b200v_nvls_allreduce_probe")
     return _rows(rows, n.value)
 
 

@@ -321,6 +321,9 @@ const char *b200v_strerror(int code) {
     case B200V_E_NONCCL: return "libnccl.so.2 not loadable";
     case B200V_E_NOMEM: return "host allocation failed";
     case B200V_E_TOOLARGE: return "size exceeds the fixed capacity of the no-allocation entry point";
+    case B200V_E_UNSUPPORTED: return "not supported by these devices or this driver";
+    case B200V_E_DRIVER: return "CUDA driver API call failed";
+    case B200V_E_TIMEOUT: return "cross-GPU barrier timed out";
     default: return "unknown b200v error";
     }
 }

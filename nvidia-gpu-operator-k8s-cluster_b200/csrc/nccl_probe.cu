@@ -13,6 +13,7 @@
 #include <nccl.h>   // types and enums only; every function is resolved with dlsym
 #include <vector>
 
+#include "ar_common.cuh"
 #include "common.cuh"
 
 namespace b200v {
@@ -76,31 +77,6 @@ const NcclApi *nccl() {
             return B200V_E_NCCL;                                  \
         }                                                         \
     } while (0)
-
-// (i+r)&7 would do for 2 and 4 ranks but sums to the constant 28 over 8 ranks; the odd multiplier
-// keeps the sum a function of i at every rank count.  Sums stay below 2^24, hence exact.
-__host__ __device__ inline float ar_value(size_t i, int r) {
-    return (float)((i * (size_t)(2 * r + 1) + (size_t)r) & 15);
-}
-
-__global__ void __launch_bounds__(256) ar_fill_kernel(float *buf, size_t n, int rank) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockDim.x * blockIdx.x + threadIdx.x; i < n; i += stride)
-        buf[i] = ar_value(i, rank);
-}
-
-// Counts elements whose bits differ from sum_{r<nranks} ar_value(i, r).
-__global__ void __launch_bounds__(256)
-ar_check_kernel(const float *buf, size_t n, int nranks, unsigned long long *bad) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    unsigned long long local = 0;
-    for (size_t i = (size_t)blockDim.x * blockIdx.x + threadIdx.x; i < n; i += stride) {
-        float want = 0.0f;
-        for (int r = 0; r < nranks; ++r) want += ar_value(i, r);
-        local += __float_as_uint(want) != __float_as_uint(buf[i]);
-    }
-    if (local) atomicAdd(bad, local);
-}
 
 struct Rank {
     int dev = -1, rank = -1;

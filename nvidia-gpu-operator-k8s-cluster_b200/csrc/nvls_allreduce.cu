@@ -1,0 +1,439 @@
+// nvls_allreduce.cu — a hand-written all-reduce over NVLink/NVSwitch multicast, as a second NVLink
+// health probe beside NCCL.  Single process, one kernel per GPU.
+//
+// How it moves data.  Every GPU's buffer is bound to one multicast object (cuMulticastCreate /
+// cuMulticastBindMem), so one address names "this offset on all GPUs".  GPU r owns slice r of the
+// vector and, for each 16 bytes of it, issues
+//     multimem.ld_reduce.add.v4.f32   -> the NVSwitch reads that offset from all N GPUs, adds, and
+//                                        returns the sum (the reduction happens in the switch)
+//     multimem.st.v4.f32              -> the switch writes the sum back to that offset on all N
+// so each GPU sends and receives about one vector's worth of bytes per all-reduce instead of the
+// 2(N-1)/N x N of a ring, and no GPU ever touches a peer's memory with ordinary loads or stores.
+// Two cross-GPU barriers bracket the work (inputs ready / results landed); they use
+// multimem.red.add on a per-CTA flag word that exists on every GPU, then spin on the local copy.
+//
+// Everything from the CUDA driver API is resolved through cudaGetDriverEntryPoint, so the library
+// keeps having no link-time dependency on libcuda.  The spin loops are bounded (B200V_NVLS_TIMEOUT_MS,
+// default 2000): a peer that never arrives yields B200V_E_TIMEOUT, never a hung GPU.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cuda.h>   // types and enums; every driver function is fetched at run time
+#include <vector>
+
+#include "ar_common.cuh"
+#include "common.cuh"
+
+namespace b200v {
+namespace {
+
+constexpr size_t kFlagBytes = 64 * 1024;      // barrier words live in front of the data
+constexpr int kMaxCtas = 4096;
+constexpr int kThreads = 512;
+
+struct Drv {
+    CUresult (*DeviceGet)(CUdevice *, int) = nullptr;
+    CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice) = nullptr;
+    CUresult (*MulticastCreate)(CUmemGenericAllocationHandle *, const CUmulticastObjectProp *) = nullptr;
+    CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
+    CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t,
+                                 size_t, unsigned long long) = nullptr;
+    CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
+    CUresult (*MulticastGetGranularity)(size_t *, const CUmulticastObjectProp *, CUmulticastGranularity_flags) = nullptr;
+    CUresult (*MemCreate)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*MemAddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*MemGetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+    bool ok = false;
+};
+
+template <typename F>
+bool drv_sym(const char *name, F &out) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess || !p) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    out = reinterpret_cast<F>(p);
+    return true;
+}
+
+const Drv &drv() {
+    static Drv d = [] {
+        Drv x;
+        x.ok = drv_sym("cuDeviceGet", x.DeviceGet) && drv_sym("cuDeviceGetAttribute", x.DeviceGetAttribute) &&
+               drv_sym("cuMulticastCreate", x.MulticastCreate) && drv_sym("cuMulticastAddDevice", x.MulticastAddDevice) &&
+               drv_sym("cuMulticastBindMem", x.MulticastBindMem) && drv_sym("cuMulticastUnbind", x.MulticastUnbind) &&
+               drv_sym("cuMulticastGetGranularity", x.MulticastGetGranularity) && drv_sym("cuMemCreate", x.MemCreate) &&
+               drv_sym("cuMemRelease", x.MemRelease) && drv_sym("cuMemAddressReserve", x.MemAddressReserve) &&
+               drv_sym("cuMemAddressFree", x.MemAddressFree) && drv_sym("cuMemMap", x.MemMap) &&
+               drv_sym("cuMemUnmap", x.MemUnmap) && drv_sym("cuMemSetAccess", x.MemSetAccess) &&
+               drv_sym("cuMemGetAllocationGranularity", x.MemGetAllocationGranularity);
+        return x;
+    }();
+    return d;
+}
+
+// ---- device side -------------------------------------------------------------------------------------
+
+__device__ __forceinline__ unsigned long long now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// All CTAs with this blockIdx on all GPUs meet here.  mc_flag names the flag word on every GPU,
+// uc_flag is this GPU's own copy.  Returns false on timeout.
+__device__ __forceinline__ bool gpu_barrier(unsigned *mc_flag, unsigned *uc_flag, unsigned target,
+                                            unsigned long long timeout_ns) {
+    __shared__ int ok_s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc_flag), "r"(1u) : "memory");
+        const unsigned long long t0 = now_ns();
+        int ok = 1;
+        unsigned polls = 0;
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(uc_flag) : "memory");
+            if ((int)(v - target) >= 0) break;
+            if ((++polls & 1023u) == 0 && now_ns() - t0 > timeout_ns) { ok = 0; break; }
+        }
+        ok_s = ok;
+    }
+    __syncthreads();
+    return ok_s != 0;
+}
+
+__device__ __forceinline__ float4 mm_ld_reduce(const float *mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void mm_st(float *mc, const float4 &r) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
+}
+
+// In-place sum all-reduce of n4 float4 vectors that live at the same offset on every GPU.
+// mc_base / uc_base: this GPU's mapping of the multicast object / of its own memory; flags first.
+template <int UNROLL>
+__global__ void __launch_bounds__(kThreads)
+nvls_allreduce_kernel(unsigned char *mc_base, unsigned char *uc_base, size_t n4, int rank, int nranks,
+                      unsigned epoch, unsigned long long timeout_ns, int *err) {
+    unsigned *mc_flag = reinterpret_cast<unsigned *>(mc_base) + blockIdx.x;
+    unsigned *uc_flag = reinterpret_cast<unsigned *>(uc_base) + blockIdx.x;
+    float *mc = reinterpret_cast<float *>(mc_base + kFlagBytes);
+
+    // (1) every GPU has entered this kernel, so every GPU's input (produced earlier on its stream)
+    //     is complete and visible
+    if (!gpu_barrier(mc_flag, uc_flag, epoch + (unsigned)nranks, timeout_ns)) {
+        if (threadIdx.x == 0) atomicExch(err, 1);
+        return;
+    }
+    const size_t per = (n4 + (size_t)nranks - 1) / (size_t)nranks;
+    const size_t lo = per * (size_t)rank < n4 ? per * (size_t)rank : n4;
+    const size_t hi = lo + per < n4 ? lo + per : n4;
+    // CTA b walks tiles b, b+grid, ... of its GPU's slice; a tile is UNROLL x kThreads float4s, and a
+    // thread issues all UNROLL switch-side reductions before the first broadcast store.
+    constexpr size_t TILE = (size_t)UNROLL * kThreads;
+    for (size_t t0 = lo + (size_t)blockIdx.x * TILE; t0 < hi; t0 += (size_t)gridDim.x * TILE) {
+        float4 acc[UNROLL];
+        if (t0 + TILE <= hi) {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) acc[j] = mm_ld_reduce(mc + 4 * (t0 + (size_t)j * kThreads + threadIdx.x));
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) mm_st(mc + 4 * (t0 + (size_t)j * kThreads + threadIdx.x), acc[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const size_t v = t0 + (size_t)j * kThreads + threadIdx.x;
+                if (v < hi) mm_st(mc + 4 * v, mm_ld_reduce(mc + 4 * v));
+            }
+        }
+    }
+
+    // (2) nobody leaves before every GPU's stores have landed everywhere
+    if (!gpu_barrier(mc_flag, uc_flag, epoch + 2u * (unsigned)nranks, timeout_ns)) {
+        if (threadIdx.x == 0) atomicExch(err, 2);
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+
+struct NvlsRank {
+    int dev = -1;
+    CUdevice cudev = 0;
+    CUmemGenericAllocationHandle mem = 0;
+    CUdeviceptr uc = 0, mc = 0;
+    bool bound = false, uc_mapped = false, mc_mapped = false;
+    cudaStream_t st = nullptr;
+    unsigned long long *d_bad = nullptr;
+    int *d_err = nullptr;
+    int sm_count = 0;
+    std::vector<cudaEvent_t> ev;
+};
+
+struct NvlsTeam {
+    std::vector<NvlsRank> ranks;
+    CUmemGenericAllocationHandle mc_handle = 0;
+    size_t size = 0;
+    bool have_mc = false;
+};
+
+#define B200V_CU(expr)                                   \
+    do {                                                 \
+        CUresult r__ = (expr);                           \
+        if (r__ != CUDA_SUCCESS) {                       \
+            g_last_cu = (int)r__;                        \
+            return r__ == CUDA_ERROR_NOT_SUPPORTED ? B200V_E_UNSUPPORTED : B200V_E_DRIVER; \
+        }                                                \
+    } while (0)
+
+int g_last_cu = 0;
+
+void destroy_team(NvlsTeam &t) {
+    const Drv &d = drv();
+    for (NvlsRank &r : t.ranks) {
+        if (r.dev < 0) continue;
+        cudaSetDevice(r.dev);
+        if (r.st) cudaStreamSynchronize(r.st);
+    }
+    for (NvlsRank &r : t.ranks) {
+        if (r.dev < 0) continue;
+        cudaSetDevice(r.dev);
+        if (r.mc_mapped) { d.MemUnmap(r.mc, t.size); }
+        if (r.mc) d.MemAddressFree(r.mc, t.size);
+        if (r.bound) d.MulticastUnbind(t.mc_handle, r.cudev, 0, t.size);
+        if (r.uc_mapped) d.MemUnmap(r.uc, t.size);
+        if (r.uc) d.MemAddressFree(r.uc, t.size);
+        if (r.mem) d.MemRelease(r.mem);
+        for (cudaEvent_t e : r.ev) cudaEventDestroy(e);
+        if (r.d_bad) cudaFree(r.d_bad);
+        if (r.d_err) cudaFree(r.d_err);
+        if (r.st) cudaStreamDestroy(r.st);
+    }
+    if (t.have_mc) d.MemRelease(t.mc_handle);
+    t.ranks.clear();
+}
+
+int build_team(NvlsTeam &t, int ndev, const int *devs, size_t data_bytes, int iters) {
+    const Drv &d = drv();
+    if (!d.ok) return B200V_E_UNSUPPORTED;
+    t.ranks.resize((size_t)ndev);
+    for (int i = 0; i < ndev; ++i) {
+        NvlsRank &r = t.ranks[(size_t)i];
+        r.dev = devs[i];
+        B200V_CUDA(cudaSetDevice(r.dev));
+        B200V_CUDA(cudaFree(nullptr));   // make sure the primary context exists
+        B200V_CU(d.DeviceGet(&r.cudev, r.dev));
+        int mc_ok = 0;
+        B200V_CU(d.DeviceGetAttribute(&mc_ok, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, r.cudev));
+        if (!mc_ok) return B200V_E_UNSUPPORTED;
+        B200V_CUDA(cudaDeviceGetAttribute(&r.sm_count, cudaDevAttrMultiProcessorCount, r.dev));
+        B200V_CUDA(cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+        B200V_CUDA(cudaMalloc(&r.d_bad, 8));
+        B200V_CUDA(cudaMalloc(&r.d_err, 4));
+        B200V_CUDA(cudaMemset(r.d_err, 0, 4));
+        r.ev.resize((size_t)iters * 2);
+        for (auto &e : r.ev) B200V_CUDA(cudaEventCreate(&e));
+    }
+
+    CUmulticastObjectProp mprop;
+    std::memset(&mprop, 0, sizeof mprop);
+    mprop.numDevices = (unsigned)ndev;
+    mprop.size = kFlagBytes + data_bytes;
+    size_t gran = 0;
+    B200V_CU(d.MulticastGetGranularity(&gran, &mprop, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+    CUmemAllocationProp aprop;
+    std::memset(&aprop, 0, sizeof aprop);
+    aprop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    aprop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    aprop.location.id = t.ranks[0].cudev;
+    size_t agran = 0;
+    B200V_CU(d.MemGetAllocationGranularity(&agran, &aprop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+    gran = std::max(gran, agran);
+    t.size = (mprop.size + gran - 1) / gran * gran;
+    mprop.size = t.size;
+    B200V_CU(d.MulticastCreate(&t.mc_handle, &mprop));
+    t.have_mc = true;
+    for (NvlsRank &r : t.ranks) B200V_CU(d.MulticastAddDevice(t.mc_handle, r.cudev));
+
+    for (NvlsRank &r : t.ranks) {
+        B200V_CUDA(cudaSetDevice(r.dev));
+        aprop.location.id = r.cudev;
+        B200V_CU(d.MemCreate(&r.mem, t.size, &aprop, 0));
+        B200V_CU(d.MulticastBindMem(t.mc_handle, 0, r.mem, 0, t.size, 0));
+        r.bound = true;
+        CUmemAccessDesc acc;
+        std::memset(&acc, 0, sizeof acc);
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = r.cudev;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        B200V_CU(d.MemAddressReserve(&r.uc, t.size, gran, 0, 0));
+        B200V_CU(d.MemMap(r.uc, t.size, 0, r.mem, 0));
+        r.uc_mapped = true;
+        B200V_CU(d.MemSetAccess(r.uc, t.size, &acc, 1));
+        B200V_CU(d.MemAddressReserve(&r.mc, t.size, gran, 0, 0));
+        B200V_CU(d.MemMap(r.mc, t.size, 0, t.mc_handle, 0));
+        r.mc_mapped = true;
+        B200V_CU(d.MemSetAccess(r.mc, t.size, &acc, 1));
+        B200V_CUDA(cudaMemsetAsync((void *)r.uc, 0, kFlagBytes, r.st));
+        B200V_CUDA(cudaStreamSynchronize(r.st));
+    }
+    return B200V_OK;
+}
+
+int grid_fill(const NvlsRank &r, size_t n) {
+    size_t g = (n + 255) / 256;
+    const size_t cap = (size_t)r.sm_count * 8;
+    if (g > cap) g = cap;
+    return g < 1 ? 1 : (int)g;
+}
+
+}  // namespace
+}  // namespace b200v
+
+using namespace b200v;
+
+extern "C" int b200v_last_driver_error(void) { return g_last_cu; }
+
+extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
+                                          int warmup, int iters, b200v_ar_row *rows, int max_rows,
+                                          int *nrows) {
+    if (ndev < 2 || !devs || !rows || !nrows || max_rows < 1 || iters < 1 || warmup < 0 || min_bytes < 16 ||
+        (min_bytes & 15) || max_bytes < min_bytes)
+        return B200V_E_BADARG;
+    *nrows = 0;
+    int count = 0;
+    int rc = b200v_device_count(&count);
+    if (rc != B200V_OK) return rc;
+    for (int i = 0; i < ndev; ++i)
+        if (devs[i] < 0 || devs[i] >= count) return B200V_E_BADARG;
+
+    NvlsTeam team;
+    struct Cleanup {
+        NvlsTeam &t;
+        ~Cleanup() { destroy_team(t); }
+    } cleanup{team};
+    rc = build_team(team, ndev, devs, max_bytes, iters);
+    if (rc != B200V_OK) return rc;
+
+    int ctas = team.ranks[0].sm_count;
+    for (const NvlsRank &r : team.ranks) ctas = std::min(ctas, r.sm_count);
+    if (const char *e = std::getenv("B200V_NVLS_CTAS")) {
+        const int v = std::atoi(e);
+        if (v >= 1 && v <= kMaxCtas) ctas = v;
+    }
+    if ((size_t)ctas * 4 > kFlagBytes) ctas = (int)(kFlagBytes / 4);
+    int unroll = 4;
+    if (const char *e = std::getenv("B200V_NVLS_UNROLL")) unroll = std::atoi(e);
+    unsigned long long timeout_ns = 2000ull * 1000000ull;
+    if (const char *e = std::getenv("B200V_NVLS_TIMEOUT_MS")) {
+        const long v = std::atol(e);
+        if (v > 0) timeout_ns = (unsigned long long)v * 1000000ull;
+    }
+
+    unsigned epoch = 0;   // every launch consumes 2*ndev counts of each flag word
+    auto allreduce_all = [&](size_t n4) -> int {
+        for (int i = 0; i < ndev; ++i) {
+            NvlsRank &r = team.ranks[(size_t)i];
+            B200V_CUDA(cudaSetDevice(r.dev));
+            auto kern = unroll == 1 ? nvls_allreduce_kernel<1> : unroll == 2 ? nvls_allreduce_kernel<2>
+                      : unroll == 8 ? nvls_allreduce_kernel<8> : nvls_allreduce_kernel<4>;
+            kern<<<ctas, kThreads, 0, r.st>>>((unsigned char *)r.mc, (unsigned char *)r.uc, n4, i, ndev, epoch,
+                                              timeout_ns, r.d_err);
+            B200V_CUDA(cudaGetLastError());
+        }
+        epoch += 2u * (unsigned)ndev;
+        return B200V_OK;
+    };
+    auto sync_and_check_err = [&]() -> int {
+        int worst = 0;
+        for (NvlsRank &r : team.ranks) {
+            B200V_CUDA(cudaSetDevice(r.dev));
+            B200V_CUDA(cudaStreamSynchronize(r.st));
+            int e = 0;
+            B200V_CUDA(cudaMemcpy(&e, r.d_err, 4, cudaMemcpyDeviceToHost));
+            worst = std::max(worst, e);
+        }
+        return worst ? B200V_E_TIMEOUT : B200V_OK;
+    };
+
+    int nr = 0;
+    for (size_t bytes = min_bytes; bytes <= max_bytes && nr < max_rows; bytes *= 2) {
+        b200v_ar_row *row = &rows[nr];
+        std::memset(row, 0, sizeof(*row));
+        row->bytes = bytes;
+        const size_t count_f = bytes / 4, n4 = bytes / 16;
+
+        for (int i = 0; i < ndev; ++i) {
+            NvlsRank &r = team.ranks[(size_t)i];
+            B200V_CUDA(cudaSetDevice(r.dev));
+            float *data = reinterpret_cast<float *>((unsigned char *)r.uc + kFlagBytes);
+            ar_fill_kernel<<<grid_fill(r, count_f), 256, 0, r.st>>>(data, count_f, i);
+            B200V_CUDA(cudaGetLastError());
+            B200V_CUDA(cudaMemsetAsync(r.d_bad, 0, 8, r.st));
+        }
+        rc = allreduce_all(n4);
+        if (rc != B200V_OK) return rc;
+        for (int i = 0; i < ndev; ++i) {
+            NvlsRank &r = team.ranks[(size_t)i];
+            B200V_CUDA(cudaSetDevice(r.dev));
+            const float *data = reinterpret_cast<const float *>((unsigned char *)r.uc + kFlagBytes);
+            ar_check_kernel<<<grid_fill(r, count_f), 256, 0, r.st>>>(data, count_f, ndev, r.d_bad);
+            B200V_CUDA(cudaGetLastError());
+        }
+        rc = sync_and_check_err();
+        if (rc != B200V_OK) return rc;
+        for (NvlsRank &r : team.ranks) {
+            B200V_CUDA(cudaSetDevice(r.dev));
+            unsigned long long bad = 0;
+            B200V_CUDA(cudaMemcpy(&bad, r.d_bad, 8, cudaMemcpyDeviceToHost));
+            row->mismatches += bad;
+        }
+
+        for (int i = 0; i < warmup; ++i) {
+            rc = allreduce_all(n4);
+            if (rc != B200V_OK) return rc;
+        }
+        for (int it = 0; it < iters; ++it) {
+            for (NvlsRank &r : team.ranks) {
+                B200V_CUDA(cudaSetDevice(r.dev));
+                B200V_CUDA(cudaEventRecord(r.ev[2 * it], r.st));
+            }
+            rc = allreduce_all(n4);
+            if (rc != B200V_OK) return rc;
+            for (NvlsRank &r : team.ranks) {
+                B200V_CUDA(cudaSetDevice(r.dev));
+                B200V_CUDA(cudaEventRecord(r.ev[2 * it + 1], r.st));
+            }
+        }
+        rc = sync_and_check_err();
+        if (rc != B200V_OK) return rc;
+        std::vector<float> ms((size_t)iters, 0.f);
+        for (int it = 0; it < iters; ++it)
+            for (NvlsRank &r : team.ranks) {
+                float t = 0.f;
+                B200V_CUDA(cudaEventElapsedTime(&t, r.ev[2 * it], r.ev[2 * it + 1]));
+                ms[(size_t)it] = std::max(ms[(size_t)it], t);
+            }
+        std::sort(ms.begin(), ms.end());
+        row->best_ms = ms[0];
+        row->median_ms = ms[(size_t)iters / 2];
+        row->algbw_gbs = (double)bytes / (row->best_ms * 1e-3) / 1e9;
+        row->busbw_gbs = row->algbw_gbs * 2.0 * (ndev - 1) / ndev;
+        ++nr;
+        if (bytes > max_bytes / 2) break;
+    }
+    *nrows = nr;
+    return B200V_OK;
+}

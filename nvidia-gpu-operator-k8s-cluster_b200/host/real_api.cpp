@@ -13,6 +13,7 @@ Api real_api() {
     a.allreduce_probe = b200v_allreduce_probe;
     a.strerror = b200v_strerror;
     a.shutdown = b200v_shutdown;
+    a.nvls_allreduce_probe = b200v_nvls_allreduce_probe;
     return a;
 }
 

@@ -141,8 +141,8 @@ bool parse_config(int argc, char **argv, Config &cfg) {
             return false;
         }
     }
-    if (cfg.mode != "validate" && cfg.mode != "stream" && cfg.mode != "nccl") {
-        cfg.error = "B200V_MODE must be validate, stream or nccl, not " + cfg.mode;
+    if (cfg.mode != "validate" && cfg.mode != "stream" && cfg.mode != "nccl" && cfg.mode != "nvls") {
+        cfg.error = "B200V_MODE must be validate, stream, nccl or nvls, not " + cfg.mode;
         return false;
     }
     return true;
@@ -605,6 +605,9 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
 }
 
 int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    // B200V_MODE=nvls runs the same sweep with the hand-written NVLink-multicast kernel.
+    const bool nvls = cfg.mode == "nvls";
+    const char *mode = nvls ? "nvls" : "nccl";
     int ndev = 0;
     int rc = api.device_count(&ndev);
     if (rc != B200V_OK || ndev < 1) {
@@ -626,37 +629,41 @@ int run_nccl_probe(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     std::fflush(nullptr);
     const int saved_fd = ::dup(1);
     if (saved_fd >= 0) ::dup2(2, 1);
-    rc = api.allreduce_probe(use, devs.data(), lo, hi, 5, 20, rows.data(), (int)rows.size(), &nrows);
+    if (nvls && !api.nvls_allreduce_probe) rc = B200V_E_BADARG;
+    else if (nvls) rc = api.nvls_allreduce_probe(use, devs.data(), std::max<size_t>(lo, 16), hi, 5, 20, rows.data(),
+                                                 (int)rows.size(), &nrows);
+    else rc = api.allreduce_probe(use, devs.data(), lo, hi, 5, 20, rows.data(), (int)rows.size(), &nrows);
     std::fflush(nullptr);
     if (saved_fd >= 0) {
         ::dup2(saved_fd, 1);
         ::close(saved_fd);
     }
     int failures = rc != B200V_OK ? 1 : 0;
-    if (rc != B200V_OK) std::fprintf(err, "nccl probe failed: %s\n", api.strerror(rc));
+    if (rc != B200V_OK) std::fprintf(err, "%s probe failed: %s\n", mode, api.strerror(rc));
     const double min_busbw = std::atof(env_or("B200V_MIN_BUSBW_GBS", "0").c_str());
-    std::string prom = "# HELP b200v_nvlink_allreduce_busbw_gbs NCCL all-reduce bus bandwidth, GB/s\n"
+    std::string prom = "# HELP b200v_nvlink_allreduce_busbw_gbs all-reduce bus bandwidth over NVLink, GB/s\n"
                        "# TYPE b200v_nvlink_allreduce_busbw_gbs gauge\n";
     for (int i = 0; i < nrows; ++i) {
         const b200v_ar_row &r = rows[(size_t)i];
         if (r.mismatches) ++failures;
         char line[256];
-        std::snprintf(line, sizeof line, "b200v_nvlink_allreduce_busbw_gbs{ranks=\"%d\",bytes=\"%" PRIu64 "\"} %.2f\n",
-                      use, r.bytes, r.busbw_gbs);
+        std::snprintf(line, sizeof line,
+                      "b200v_nvlink_allreduce_busbw_gbs{impl=\"%s\",ranks=\"%d\",bytes=\"%" PRIu64 "\"} %.2f\n", mode, use,
+                      r.bytes, r.busbw_gbs);
         prom += line;
         std::fprintf(out,
-                     "{\"mode\":\"nccl\",\"ranks\":%d,\"bytes\":%" PRIu64 ",\"best_ms\":%.5f,\"median_ms\":%.5f,"
+                     "{\"mode\":\"%s\",\"ranks\":%d,\"bytes\":%" PRIu64 ",\"best_ms\":%.5f,\"median_ms\":%.5f,"
                      "\"algbw_gbs\":%.2f,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%" PRIu64 "}\n",
-                     use, r.bytes, r.best_ms, r.median_ms, r.algbw_gbs, r.busbw_gbs, r.busbw_gbs / 900.0,
+                     mode, use, r.bytes, r.best_ms, r.median_ms, r.algbw_gbs, r.busbw_gbs, r.busbw_gbs / 900.0,
                      r.mismatches);
     }
     if (nrows > 0 && min_busbw > 0 && rows[(size_t)nrows - 1].busbw_gbs < min_busbw) {
-        std::fprintf(err, "nccl probe failed: busBW %.1f GB/s below the required %.1f GB/s\n",
+        std::fprintf(err, "%s probe failed: busBW %.1f GB/s below the required %.1f GB/s\n", mode,
                      rows[(size_t)nrows - 1].busbw_gbs, min_busbw);
         ++failures;
     }
     std::fflush(out);
-    if (!failures) write_prom(cfg, "nvlink-busbw.prom", prom);
+    if (!failures) write_prom(cfg, nvls ? "nvlink-busbw-nvls.prom" : "nvlink-busbw.prom", prom);
     return failures ? 1 : 0;
 }
 
@@ -669,7 +676,7 @@ int validator_main(const Api &api, int argc, char **argv) {
         return 1;
     }
     if (cfg.mode == "stream") return run_stream_sweep(api, cfg, stdout, stderr);
-    if (cfg.mode == "nccl") return run_nccl_probe(api, cfg, stdout, stderr);
+    if (cfg.mode == "nccl" || cfg.mode == "nvls") return run_nccl_probe(api, cfg, stdout, stderr);
     if (cfg.component.empty()) {
         std::fprintf(stderr, "invalid -c <component-name> flag: must not be empty string\n");
         return 1;

@@ -31,6 +31,7 @@ struct Api {
     int (*allreduce_probe)(int, const int *, size_t, size_t, int, int, b200v_ar_row *, int, int *);
     const char *(*strerror)(int);
     int (*shutdown)(void);
+    int (*nvls_allreduce_probe)(int, const int *, size_t, size_t, int, int, b200v_ar_row *, int, int *);
 };
 
 // The table bound to libb200validate.so (real_api.cpp; linked only into the product binaries).

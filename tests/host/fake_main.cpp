@@ -103,7 +103,7 @@ int fake_shutdown(void) { return 0; }
 
 int main(int argc, char **argv) {
     b200v_host::Api api{fake_device_count, fake_device_info, fake_vectoradd, fake_stream,
-                        fake_allreduce,    fake_strerror,    fake_shutdown};
+                        fake_allreduce,    fake_strerror,    fake_shutdown,    fake_allreduce};
     const char *entry = std::getenv("FAKE_ENTRY");
     if (entry && !std::strcmp(entry, "vectoradd")) return b200v_host::vectoradd_main(api, argc, argv);
     return b200v_host::validator_main(api, argc, argv);

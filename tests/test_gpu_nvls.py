@@ -1,0 +1,35 @@
+"""GPU test of the hand-written NVLink-multicast all-reduce probe: bit-exact
+against the closed form at every size, and in agreement with the NCCL probe's row format.
+Needs at least two GPUs with multicast (NVSwitch) support; skipped otherwise."""
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_nvls_allreduce_probe_bit_exact(capi, gpu):
+    if gpu < 2:
+        pytest.skip("needs at least two GPUs")
+    try:
+        rows = capi.nvls_allreduce_probe(list(range(gpu)), min_bytes=1 << 10, max_bytes=1 << 26, warmup=2, iters=5)
+    except capi.B200VError as e:
+        if e.code == capi.E_UNSUPPORTED:
+            pytest.skip("no multicast support on this box")
+        raise
+    assert [r.bytes for r in rows] == [1 << k for k in range(10, 27)]
+    assert all(r.mismatches == 0 for r in rows)              # exact sum, every element, every GPU
+    top = rows[-1]
+    assert top.best_ms > 0 and top.best_ms <= top.median_ms
+    assert abs(top.busbw_gbs - top.algbw_gbs * 2 * (gpu - 1) / gpu) < 1e-6
+    assert top.busbw_gbs > 50.0
+
+
+def test_nvls_probe_argument_checks(capi, gpu):
+    with pytest.raises(capi.B200VError) as ei:
+        capi.nvls_allreduce_probe([0], min_bytes=1024, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG                    # one GPU is not a collective
+    with pytest.raises(capi.B200VError) as ei:
+        capi.nvls_allreduce_probe([0, gpu + 3], min_bytes=1024, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG
+    with pytest.raises(capi.B200VError) as ei:
+        capi.nvls_allreduce_probe([0, 0], min_bytes=8, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG                    # sizes are multiples of 16 bytes

@@ -226,7 +226,10 @@ def test_metrics_oneshot_reflects_status_files_and_bandwidth(fake, tmp_path):
     assert 'b200v_node_cuda_gpu_ready{gpu="0"} 1' in lines and 'b200v_node_cuda_gpu_ready{gpu="1"} 1' in lines
     assert "gpu_operator_node_device_plugin_devices_total 2" in lines
     assert any(l.startswith('b200v_hbm_bandwidth_gbs{gpu="0",op="triad",log2_n="28"} ') for l in lines)
-    assert 'b200v_nvlink_allreduce_busbw_gbs{ranks="8",bytes="2048"} 700.00' in lines
+    assert 'b200v_nvlink_allreduce_busbw_gbs{impl="nccl",ranks="8",bytes="2048"} 700.00' in lines
+    # the hand-written NVLink-multicast probe is the same sweep under B200V_MODE=nvls
+    rc, out2, _err = run(fake, tmp_path, B200V_MODE="nvls", FAKE_NDEV=8, B200V_MIN_LOG2=10, B200V_MAX_LOG2=11)
+    assert rc == 0 and [json.loads(l)["mode"] for l in out2.splitlines()] == ["nvls", "nvls"]
     # every sample line is `name{labels} value` or `name value`, every family has HELP and TYPE
     for l in lines:
         assert l.startswith("#") or len(l.rsplit(" ", 1)) == 2
