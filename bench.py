@@ -374,7 +374,7 @@ def main():
         oracle = entry.load_oracle()
         oracle.build()
         del hA, hB, hC
-        passes = 6
+        passes = 40           # ~10 s of single-thread CPU work at ~0.25 s per pass
         best, med, times = cpu_verify_loop(n, 1, passes, oracle)
         cpu = {"value": round(med, 3), "best": round(best, 3), "unit": UNIT, "cores": 1, "kind": "port",
                "host_cores_available": os.cpu_count(),
