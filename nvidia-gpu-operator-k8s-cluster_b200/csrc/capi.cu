@@ -182,6 +182,19 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
         c.k_ev.push_back(e);
     }
 
+    // Whatever path leaves this function, nothing enqueued here may still be touching the caller's
+    // host buffers afterwards: drain the three streams on every exit (a no-op after the normal
+    // synchronisation below).
+    struct Drain {
+        DeviceCtx &c;
+        ~Drain() {
+            cudaStreamSynchronize(c.s_in);
+            cudaStreamSynchronize(c.s_k);
+            cudaStreamSynchronize(c.s_out);
+            (void)cudaGetLastError();
+        }
+    } drain{c};
+
     int grid = 0, block = 0;
     B200V_CUDA(cudaEventRecord(c.t_begin, c.s_in));
     B200V_CUDA(cudaStreamWaitEvent(c.s_k, c.t_begin, 0));

@@ -28,8 +28,11 @@ def pkg():
 
 @pytest.fixture(scope="session")
 def capi(pkg):
-    """The ctypes binding with the shared library loaded.  No skip when the .so is missing: the
-    product has no fallback, so a missing build is a failure."""
+    """The ctypes binding with the shared library loaded.  A missing .so is built (nvcc) — never
+    skipped or substituted: the product has no fallback, so if it cannot be built the test fails."""
+    if not os.path.exists(pkg.capi.LIB_PATH):
+        import subprocess
+        subprocess.check_call(["make", "-s", "-C", entry.PKG_DIR, "lib", "host"])
     pkg.capi.lib()
     return pkg.capi
 
