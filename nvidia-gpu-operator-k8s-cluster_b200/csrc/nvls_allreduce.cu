@@ -327,7 +327,10 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
     rc = build_team(team, ndev, devs, max_bytes, iters);
     if (rc != B200V_OK) return rc;
 
-    int ctas = team.ranks[0].sm_count;
+    // Few CTAs are enough to keep the NVLink ports busy, and more only add barrier traffic and
+    // switch-side contention: measured on 8 x B200 (busBW GB/s at 16 MiB / 64 MiB / 1 GiB)
+    //   16 CTAs 458 / 697 / 839     48 CTAs 407 / 666 / 838     148 CTAs 419 / 590 / 829
+    int ctas = 16;
     for (const NvlsRank &r : team.ranks) ctas = std::min(ctas, r.sm_count);
     if (const char *e = std::getenv("B200V_NVLS_CTAS")) {
         const int v = std::atoi(e);

@@ -15,13 +15,16 @@ hi = 1 << int(os.environ.get("B200V_MAX_LOG2", "30"))
 devs = list(range(n))
 nvls = capi.nvls_allreduce_probe(devs, min_bytes=lo, max_bytes=hi, warmup=5, iters=20)
 sys.stdout.flush()
-saved = os.dup(1)
-os.dup2(2, 1)                      # NCCL prints its banner on stdout
-try:
-    nccl = capi.allreduce_probe(devs, min_bytes=lo, max_bytes=hi, warmup=5, iters=20)
-finally:
-    os.dup2(saved, 1)
-    os.close(saved)
+if os.environ.get("B200V_SKIP_NCCL"):
+    nccl = [capi.ArRow() for _ in nvls]
+else:
+    saved = os.dup(1)
+    os.dup2(2, 1)                      # NCCL prints its banner on stdout
+    try:
+        nccl = capi.allreduce_probe(devs, min_bytes=lo, max_bytes=hi, warmup=5, iters=20)
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
 for a, b in zip(nvls, nccl):
     print(json.dumps({"ranks": n, "bytes": int(a.bytes), "nvls_ms": round(a.best_ms, 5),
                       "nvls_busbw_gbs": round(a.busbw_gbs, 2), "nvls_mismatches": int(a.mismatches),
