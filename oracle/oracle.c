@@ -93,10 +93,14 @@ static inline uint64_t mix64(uint64_t z) {
     return z ^ (z >> 31);
 }
 
-uint64_t oracle_digest(const uint32_t *w, size_t n) {
+uint64_t oracle_digest(const uint32_t *w, size_t n) { return oracle_digest_from(w, n, 0); }
+
+/* The digest is a plain sum over elements, so an array can be digested in pieces: the digest of
+ * the whole is the sum (mod 2^64) of oracle_digest_from(piece, len, index of its first element). */
+uint64_t oracle_digest_from(const uint32_t *w, size_t n, uint64_t first_index) {
     uint64_t acc = 0;
     for (size_t i = 0; i < n; ++i)
-        acc += mix64((uint64_t)w[i] + 0x9E3779B97F4A7C15ull * ((uint64_t)i + 1));
+        acc += mix64((uint64_t)w[i] + 0x9E3779B97F4A7C15ull * (first_index + (uint64_t)i + 1));
     return acc;
 }
 

@@ -56,6 +56,8 @@ uint64_t oracle_fnv1a64_words(const uint32_t *w, size_t n);
 /* Order-independent, position-sensitive digest used for device-side checks at sizes where an
  * FNV chain would serialise: sum over i of mix64(w[i] + GOLDEN*(i+1)) mod 2^64. */
 uint64_t oracle_digest(const uint32_t *w, size_t n);
+/* Same, for a piece of a larger array whose first word has index first_index; pieces add up. */
+uint64_t oracle_digest_from(const uint32_t *w, size_t n, uint64_t first_index);
 
 /* All-reduce probe closed form: rank r holds (float)((i*(2r+1) + r) & 15);
  * the sum over nranks is an exactly representable integer.  (SURVEY's (i+r)&7 sums to the

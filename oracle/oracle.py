@@ -55,6 +55,8 @@ def lib():
         L.oracle_fnv1a64_words.restype = ctypes.c_uint64
         L.oracle_digest.argtypes = [_u32p, ctypes.c_size_t]
         L.oracle_digest.restype = ctypes.c_uint64
+        L.oracle_digest_from.argtypes = [_u32p, ctypes.c_size_t, ctypes.c_uint64]
+        L.oracle_digest_from.restype = ctypes.c_uint64
         L.oracle_allreduce_expected.argtypes = [ctypes.c_size_t, ctypes.c_int]
         L.oracle_allreduce_expected.restype = ctypes.c_float
         _lib = L
@@ -120,6 +122,11 @@ def fnv1a64_words(a):
 
 def digest(a):
     return int(lib().oracle_digest(_words(a), a.size))
+
+
+def digest_from(a, first_index):
+    """Digest of a piece of a larger array; the pieces' digests add up modulo 2^64."""
+    return int(lib().oracle_digest_from(_words(a), a.size, first_index))
 
 
 def allreduce_expected(n, nranks):

@@ -188,6 +188,13 @@ def test_allreduce_closed_form(oracle, golden):
         assert len(set(oracle.allreduce_expected(64, nr).tolist())) > 2
 
 
+def test_digest_of_pieces_adds_up(oracle):
+    x = oracle.fill_hash(10007, 3)
+    for cut in (0, 1, 4000, 10006, 10007):
+        assert (oracle.digest_from(x[:cut], 0) + oracle.digest_from(x[cut:], cut)) % 2**64 == oracle.digest(x)
+    assert oracle.digest_from(x, 5) != oracle.digest(x)          # the index is part of the digest
+
+
 def test_threaded_vadd_matches_scalar(oracle):
     A = oracle.fill_hash(100003, 11)
     B = oracle.fill_hash(100003, 12)
