@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "copy_pool.h"
 #include "ew_kernels.cuh"
 
 namespace b200v {
@@ -65,10 +66,44 @@ int ensure_slots(DeviceCtx &c, size_t elems) {
     return B200V_OK;
 }
 
+void free_stage(DeviceCtx &c) {
+    for (int i = 0; i < kSlots; ++i) {
+        if (c.stage_x[i]) cudaFreeHost(c.stage_x[i]);
+        if (c.stage_y[i]) cudaFreeHost(c.stage_y[i]);
+        if (c.stage_d[i]) cudaFreeHost(c.stage_d[i]);
+        c.stage_x[i] = c.stage_y[i] = c.stage_d[i] = nullptr;
+    }
+    c.stage_elems = 0;
+}
+
+int ensure_stage(DeviceCtx &c, size_t elems) {
+    if (c.stage_elems >= elems) return B200V_OK;
+    free_stage(c);
+    for (int i = 0; i < kSlots; ++i) {
+        B200V_CUDA(cudaHostAlloc((void **)&c.stage_x[i], elems * 4, cudaHostAllocPortable));
+        B200V_CUDA(cudaHostAlloc((void **)&c.stage_y[i], elems * 4, cudaHostAllocPortable));
+        B200V_CUDA(cudaHostAlloc((void **)&c.stage_d[i], elems * 4, cudaHostAllocPortable));
+    }
+    c.stage_elems = elems;
+    return B200V_OK;
+}
+
+// True when the DMA engines can read/write this host pointer directly (cudaHostAlloc /
+// cudaHostRegister memory); false for ordinary pageable memory.
+bool is_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
 void destroy_ctx(DeviceCtx &c) {
     if (!c.ready) return;
     cudaSetDevice(c.dev);
     free_slots(c);
+    free_stage(c);
     for (int i = 0; i < kSlots; ++i) {
         cudaEventDestroy(c.in_done[i]);
         cudaEventDestroy(c.k_done[i]);
@@ -160,7 +195,11 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
         const int lg = e && *e ? std::atoi(e) : 0;
         return (lg >= 10 && lg <= 30) ? (size_t)1 << lg : kChunkElems;
     }();
-    const size_t chunk = std::min(n, chunk_cap);
+    // Pageable buffers (malloc, Go slices, numpy) are staged through pinned memory by a pool of
+    // host threads, one chunk ahead of the DMA; pinned buffers are handed to the DMA directly.
+    const bool pg_x = !is_pinned(hX), pg_y = needs_y && !is_pinned(hY), pg_d = !is_pinned(hDst);
+    const bool staged = (pg_x || pg_y || pg_d) && !std::getenv("B200V_NO_STAGING");
+    const size_t chunk = std::min(n, staged && !std::getenv("B200V_CHUNK_LOG2") ? kStagedChunkElems : chunk_cap);
     // Chunk schedule: full-size chunks, then a geometric taper (each chunk at most half of what is
     // left, down to kMinChunkElems).  The H2D stream is the bottleneck and runs back to back from
     // t = 0, so the call ends one kernel + one D2H after the LAST chunk lands: keeping that last
@@ -176,6 +215,11 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
     const size_t nchunks = sched.size();
     rc = ensure_slots(c, chunk);
     if (rc != B200V_OK) return rc;
+    if (staged) {
+        rc = ensure_stage(c, chunk);
+        if (rc != B200V_OK) return rc;
+    }
+    CopyPool &pool = CopyPool::instance();
     while (c.k_ev.size() < 2 * nchunks) {
         cudaEvent_t e;
         B200V_CUDA(cudaEventCreate(&e));
@@ -202,12 +246,28 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
     for (size_t k = 0; k < nchunks; ++k) {
         const int slot = (int)(k % kSlots);
         const size_t lo = sched[k].first, len = sched[k].second;
+        const float *src_x = hX + lo, *src_y = needs_y ? hY + lo : nullptr;
+        float *dst_h = hDst + lo;
+        if (staged) {
+            if (k >= (size_t)kSlots) {
+                // this slot's staging buffers still belong to chunk k - kSlots: its result must be
+                // handed to the caller, and its H2D must be off the wire, before they are reused
+                if (pg_d) {
+                    B200V_CUDA(cudaEventSynchronize(c.out_done[slot]));
+                    pool.copy(hDst + sched[k - kSlots].first, c.stage_d[slot], sched[k - kSlots].second * 4);
+                }
+                if (pg_x || pg_y) B200V_CUDA(cudaEventSynchronize(c.in_done[slot]));
+            }
+            if (pg_x) { pool.copy(c.stage_x[slot], hX + lo, len * 4); src_x = c.stage_x[slot]; }
+            if (pg_y) { pool.copy(c.stage_y[slot], hY + lo, len * 4); src_y = c.stage_y[slot]; }
+            if (pg_d) dst_h = c.stage_d[slot];
+        }
         // inputs of this slot are free once the kernel that read them (chunk k - kSlots) is done
         if (k >= (size_t)kSlots) B200V_CUDA(cudaStreamWaitEvent(c.s_in, c.k_done[slot], 0));
         if (k == 0) B200V_CUDA(cudaEventRecord(c.h2d_first, c.s_in));
-        B200V_CUDA(cudaMemcpyAsync(c.slot_x[slot], hX + lo, len * 4, cudaMemcpyHostToDevice, c.s_in));
+        B200V_CUDA(cudaMemcpyAsync(c.slot_x[slot], src_x, len * 4, cudaMemcpyHostToDevice, c.s_in));
         if (needs_y)
-            B200V_CUDA(cudaMemcpyAsync(c.slot_y[slot], hY + lo, len * 4, cudaMemcpyHostToDevice, c.s_in));
+            B200V_CUDA(cudaMemcpyAsync(c.slot_y[slot], src_y, len * 4, cudaMemcpyHostToDevice, c.s_in));
         B200V_CUDA(cudaEventRecord(c.in_done[slot], c.s_in));
         if (k + 1 == nchunks) B200V_CUDA(cudaEventRecord(c.h2d_last, c.s_in));
 
@@ -224,11 +284,18 @@ int host_pipeline(int dev, int op, float *hDst, const float *hX, const float *hY
 
         B200V_CUDA(cudaStreamWaitEvent(c.s_out, c.k_done[slot], 0));
         if (k == 0) B200V_CUDA(cudaEventRecord(c.d2h_first, c.s_out));
-        B200V_CUDA(cudaMemcpyAsync(hDst + lo, c.slot_d[slot], len * 4, cudaMemcpyDeviceToHost, c.s_out));
+        B200V_CUDA(cudaMemcpyAsync(dst_h, c.slot_d[slot], len * 4, cudaMemcpyDeviceToHost, c.s_out));
         B200V_CUDA(cudaEventRecord(c.out_done[slot], c.s_out));
     }
     B200V_CUDA(cudaEventRecord(c.d2h_last, c.s_out));
     B200V_CUDA(cudaEventRecord(c.t_end, c.s_out));
+    if (staged && pg_d) {   // hand over the results still sitting in the staging ring, oldest first
+        for (size_t k = nchunks > (size_t)kSlots ? nchunks - kSlots : 0; k < nchunks; ++k) {
+            const int slot = (int)(k % kSlots);
+            B200V_CUDA(cudaEventSynchronize(c.out_done[slot]));
+            pool.copy(hDst + sched[k].first, c.stage_d[slot], sched[k].second * 4);
+        }
+    }
     B200V_CUDA(cudaStreamSynchronize(c.s_out));
     B200V_CUDA(cudaStreamSynchronize(c.s_k));
     B200V_CUDA(cudaStreamSynchronize(c.s_in));

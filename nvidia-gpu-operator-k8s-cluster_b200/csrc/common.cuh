@@ -26,6 +26,9 @@ namespace b200v {
 // 2^26 -> 45.3 ms for a 2^28-element call); the ring then holds 3 x 3 x 64 MiB = 576 MiB.
 constexpr size_t kChunkElems = (size_t)1 << 24;
 constexpr size_t kMinChunkElems = (size_t)1 << 20;   // tail of the taper (4 MiB)
+// Pageable callers are staged through pinned memory by host threads; smaller chunks keep the
+// pinned footprint (3 x 3 x 16 MiB) and the first-chunk latency down.
+constexpr size_t kStagedChunkElems = (size_t)1 << 22;
 constexpr int kSlots = 3;
 
 struct DeviceCtx {
@@ -37,6 +40,9 @@ struct DeviceCtx {
     // ring slots for the host path (allocated on first use, sized to min(n, kChunkElems))
     float *slot_x[kSlots] = {}, *slot_y[kSlots] = {}, *slot_d[kSlots] = {};
     size_t slot_elems = 0;
+    // pinned host staging for callers whose buffers are pageable (allocated on first such call)
+    float *stage_x[kSlots] = {}, *stage_y[kSlots] = {}, *stage_d[kSlots] = {};
+    size_t stage_elems = 0;
     cudaEvent_t in_done[kSlots] = {}, k_done[kSlots] = {}, out_done[kSlots] = {};
     cudaEvent_t t_begin = nullptr, t_end = nullptr, h2d_first = nullptr, h2d_last = nullptr,
                 d2h_first = nullptr, d2h_last = nullptr;
