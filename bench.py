@@ -314,6 +314,23 @@ def main():
         if not torch.equal((hA[sl] + hB[sl]) + 0.0, hC[sl]):
             raise SystemExit("rank %d: e2e result mismatch" % rank)
 
+    # the same call with ordinary pageable buffers (what malloc, a Go slice or numpy hands over):
+    # the library stages them through pinned memory with a host copy pool
+    e2e_pageable = None
+    if world == 1:
+        import numpy as np
+        pA, pB = hA.numpy().copy(), hB.numpy().copy()
+        pC = np.empty(n, np.float32)
+        capi.vectoradd(pA, pB, pC, n, dev=dev)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            capi.vectoradd(pA, pB, pC, n, dev=dev)
+        e2e_pageable = {"value": round(3 * bytes_step / (time.perf_counter() - t0) / 1e9, 2), "unit": UNIT,
+                        "steps": 3, "note": "pageable host buffers, staged by the library"}
+        if pC[:k].tobytes() != hC[:k].numpy().tobytes():
+            raise SystemExit("pageable e2e result mismatch")
+        del pA, pB, pC
+
     # ---- NVLink probe (only place NCCL is used by the product) -----------------------------------
     allreduce = None
     if world > 1 and not args.no_allreduce:
@@ -398,6 +415,8 @@ def main():
                         "api": "b200v_vectoradd (pinned host buffers, chunked 3-stream pipeline)"},
                 "gpu_launches": steps * world, "e2e_gpu_launches": e2e_launches * world,
                 "clocks": clocks}
+        if e2e_pageable:
+            line["e2e_pageable"] = e2e_pageable
         if cpu:
             line["cpu_baseline"] = cpu
         if allreduce:

@@ -64,7 +64,9 @@ private:
 
     CopyPool() {
         unsigned hw = std::thread::hardware_concurrency();
-        nthreads_ = (int)std::min(8u, std::max(1u, hw / 2));
+        // measured on a 16-vCPU B200 host, 2^28-element call: 4 threads 35, 8 -> 48, 12 -> 56,
+        // 16 -> 51 GB/s end to end
+        nthreads_ = (int)std::min(12u, std::max(1u, hw * 3 / 4));
         if (const char *e = std::getenv("B200V_COPY_THREADS")) {
             const int v = std::atoi(e);
             if (v >= 1 && v <= 64) nthreads_ = v;
