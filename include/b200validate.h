@@ -90,7 +90,9 @@ typedef struct b200v_stream_result {
     uint64_t first_mismatch;           /* element index, valid when mismatches > 0 */
     int      l2_resident;              /* 1 when the op's working set fits the device L2 */
     int      grid, block;
-    int      kernel_launches;          /* timed launches of the op kernel */
+    int      kernel_launches;          /* timed launches of the op kernel: iters x the batch size
+                                          (small arrays are timed as batches of back-to-back
+                                          launches lasting >= ~200 us; times are per launch) */
 } b200v_stream_result;
 
 typedef struct b200v_ar_row {

@@ -549,10 +549,18 @@ int b200v_stream(int dev, int op, size_t n, float s, uint64_t seed, int warmup, 
         std::vector<cudaEvent_t> &v;
         ~EvFree() { for (auto e : v) cudaEventDestroy(e); }
     } evfree{ev};
+    // A launch of a small array lasts a few microseconds, comparable to the gap between two
+    // launches and to the resolution of an event pair.  Each timed sample is therefore `reps`
+    // back-to-back launches sized to last >= ~200 us (one launch once the array is large), and the
+    // sample's time is divided by reps.
+    const double est_us = (double)n * ew_bytes_per_elem(op) / 5.0e6 + 2.0;   // at ~5 TB/s, + launch
+    const int reps = (int)std::min(256.0, std::max(1.0, 200.0 / est_us));
     for (int i = 0; i < iters; ++i) {
         B200V_CUDA(cudaEventRecord(ev[2 * i], st));
-        rc = launch_ew(c, op, (float *)d.p, (const float *)x.p, (const float *)y.p, s, n, st, &r->grid, &r->block);
-        if (rc != B200V_OK) return rc;
+        for (int k = 0; k < reps; ++k) {
+            rc = launch_ew(c, op, (float *)d.p, (const float *)x.p, (const float *)y.p, s, n, st, &r->grid, &r->block);
+            if (rc != B200V_OK) return rc;
+        }
         B200V_CUDA(cudaEventRecord(ev[2 * i + 1], st));
     }
     B200V_CUDA(cudaStreamSynchronize(st));
@@ -560,6 +568,7 @@ int b200v_stream(int dev, int op, size_t n, float s, uint64_t seed, int warmup, 
     double sum = 0;
     for (int i = 0; i < iters; ++i) {
         B200V_CUDA(cudaEventElapsedTime(&ms[i], ev[2 * i], ev[2 * i + 1]));
+        ms[i] /= (float)reps;
         sum += ms[i];
     }
     std::sort(ms.begin(), ms.end());
@@ -569,7 +578,7 @@ int b200v_stream(int dev, int op, size_t n, float s, uint64_t seed, int warmup, 
     r->bytes_per_launch = (uint64_t)n * (uint64_t)ew_bytes_per_elem(op);
     r->best_gbs = (double)r->bytes_per_launch / (r->best_ms * 1e-3) / 1e9;
     r->median_gbs = (double)r->bytes_per_launch / (r->median_ms * 1e-3) / 1e9;
-    r->kernel_launches = iters;
+    r->kernel_launches = iters * reps;
     r->l2_resident = ((size_t)(needs_y ? 3 : 2) * n * 4 <= c.l2_bytes) ? 1 : 0;
 
     rc = check_impl(c, op, (const float *)d.p, (const float *)x.p, (const float *)y.p, s, n,

@@ -192,7 +192,9 @@ def test_stream_row(capi, oracle, gpu, name):
     assert r.mismatches == 0
     assert r.digest == oracle.digest(oracle.stream(op_id(oracle, name), x, y, 3.0))
     assert r.bytes_per_launch == n * capi.OP_BYTES_PER_ELEM[op_id(capi, name)]
-    assert r.kernel_launches == 5 and r.best_ms > 0 and r.best_ms <= r.median_ms
+    # small arrays are timed as batches of back-to-back launches: a multiple of the 5 samples
+    assert r.kernel_launches >= 5 and r.kernel_launches % 5 == 0
+    assert r.best_ms > 0 and r.best_ms <= r.median_ms
     assert r.l2_resident == 1
 
 
