@@ -203,6 +203,14 @@ func validateCuda(c *config) int {
 	for _, f := range old {
 		os.Remove(f)
 	}
+	if !c.withWorkload { // upstream: no workload, just (re)create the status file
+		if err := createStatusFile(c, "cuda-ready"); err != nil {
+			fmt.Fprintf(os.Stderr, "unable to create status file %s: %v\n", statusPath(c, "cuda-ready"), err)
+			return 1
+		}
+		fmt.Println("cuda workload validation is disabled (WITH_WORKLOAD=false)")
+		return 0
+	}
 	var ndev C.int
 	if rc := C.b200v_device_count(&ndev); rc != 0 || ndev < 1 {
 		fmt.Fprintf(os.Stderr, "cuda validation failed: %s\n", strerror(rc))

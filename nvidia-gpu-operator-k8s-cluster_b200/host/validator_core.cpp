@@ -284,6 +284,17 @@ int validate_cuda(const Api &api, const Config &cfg, FILE *out, FILE *err) {
                      std::strerror(errno));
         return 1;
     }
+    if (!cfg.with_workload) {
+        // Upstream's behaviour with WITH_WORKLOAD=false: no workload is run, the status file is
+        // simply (re)created so the next init container is not blocked.
+        if (!create_status_file(cfg, "cuda-ready")) {
+            std::fprintf(err, "unable to create status file %s: %s\n", status_path(cfg, "cuda-ready").c_str(),
+                         std::strerror(errno));
+            return 1;
+        }
+        std::fprintf(out, "cuda workload validation is disabled (WITH_WORKLOAD=false)\n");
+        return 0;
+    }
     int ndev = 0;
     int rc = api.device_count(&ndev);
     if (rc != B200V_OK || ndev < 1) {

@@ -63,6 +63,13 @@ def test_cuda_failure_removes_stale_status_and_exits_1(fake, tmp_path):
     assert ready(tmp_path) == ["driver-ready"]
 
 
+def test_with_workload_false_only_writes_the_status_file(fake, tmp_path):
+    (tmp_path / "cuda-gpu3-ready").write_text("")      # stale per-GPU file from an earlier run
+    rc, out, _err = run(fake, tmp_path, COMPONENT="cuda", WITH_WORKLOAD="false", FAKE_NDEV=0)
+    assert rc == 0 and "disabled" in out and "Vector addition" not in out
+    assert ready(tmp_path) == ["cuda-ready"]
+
+
 def test_cuda_error_from_library_is_reported(fake, tmp_path):
     rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_MODE="cudaerr")
     assert rc == 1 and "illegal memory access" in err
