@@ -220,7 +220,9 @@ int b200v_last_nccl_error(void);
 /* A second, hand-written NVLink probe (nothing upstream): the same sweep, input
  * pattern, bit-exact check and row format as b200v_allreduce_probe, but the all-reduce is one
  * sm_100a kernel per GPU that reduces inside the NVSwitch (multimem.ld_reduce) and broadcasts
- * through it (multimem.st) over a CUDA multicast object.  Single process, 2 <= ndev, sizes are
+ * through it (multimem.st) over a CUDA multicast object; with 2 GPUs, where the switch has
+ * nothing to reduce, the kernel uses plain peer loads/stores over NVLink instead
+ * (B200V_NVLS_ALGO=multimem|p2p forces either).  Single process, 2 <= ndev, sizes are
  * multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast
  * support, B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
 int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,

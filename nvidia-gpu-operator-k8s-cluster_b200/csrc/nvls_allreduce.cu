@@ -12,6 +12,10 @@
 // Two cross-GPU barriers bracket the work (inputs ready / results landed); they use
 // multimem.red.add on a per-CTA flag word that exists on every GPU, then spin on the local copy.
 //
+// With 2 GPUs the switch has nothing to reduce and a second kernel is used instead
+// (p2p_allreduce_kernel below): plain peer loads and stores over NVLink, same slicing, same
+// barriers.  B200V_NVLS_ALGO=multimem|p2p forces either.
+//
 // Everything from the CUDA driver API is resolved through cudaGetDriverEntryPoint, so the library
 // keeps having no link-time dependency on libcuda.  The spin loops are bounded (B200V_NVLS_TIMEOUT_MS,
 // default 2000): a peer that never arrives yields B200V_E_TIMEOUT, never a hung GPU.
@@ -167,6 +171,86 @@ nvls_allreduce_kernel(unsigned char *mc_base, unsigned char *uc_base, size_t n4,
     }
 }
 
+// The same all-reduce with plain peer loads and stores over NVLink instead of switch-side
+// reduction: GPU r reads slice r from every GPU (N-1 of them across NVLink), adds in rank order,
+// and stores the sum into slice r of every GPU.  Each GPU then moves 2(N-1)/N x S per direction —
+// what a ring moves, but in one hop and with no per-step synchronisation — which beats the
+// multicast form at 2 GPUs (683 vs 394 GB/s), where the switch has nothing to reduce and the
+// multicast form still sends the local copy on a round trip through it.  From 4 GPUs the
+// multicast form is ahead (678 vs 661 GB/s at 4).
+constexpr int kMaxPeers = 8;
+struct PeerPtrs {
+    float *data[kMaxPeers];
+};
+
+// STRONG = .relaxed.sys accesses; otherwise ordinary weak ones.  Weak is safe here: inputs were
+// complete before the opening barrier (acquire.sys + bar.sync), nothing in this kernel has read
+// these lines before (L1 is invalidated at launch), and the closing barrier's release.sys follows
+// a __threadfence_system().
+template <bool STRONG>
+__device__ __forceinline__ float4 ld_f4(const float *p) {
+    float4 r;
+    if constexpr (STRONG)
+        asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    else
+        asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+template <bool STRONG>
+__device__ __forceinline__ void st_f4(float *p, const float4 &r) {
+    if constexpr (STRONG)
+        asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
+    else
+        asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
+}
+
+template <int NR, int UNROLL, bool STRONG>
+__global__ void __launch_bounds__(kThreads)
+p2p_allreduce_kernel(PeerPtrs peers, unsigned char *mc_base, unsigned char *uc_base, size_t n4, int rank,
+                     unsigned epoch, unsigned long long timeout_ns, int *err) {
+    unsigned *mc_flag = reinterpret_cast<unsigned *>(mc_base) + blockIdx.x;
+    unsigned *uc_flag = reinterpret_cast<unsigned *>(uc_base) + blockIdx.x;
+    if (!gpu_barrier(mc_flag, uc_flag, epoch + (unsigned)NR, timeout_ns)) {
+        if (threadIdx.x == 0) atomicExch(err, 1);
+        return;
+    }
+    const size_t per = (n4 + (size_t)NR - 1) / (size_t)NR;
+    const size_t lo = per * (size_t)rank < n4 ? per * (size_t)rank : n4;
+    const size_t hi = lo + per < n4 ? lo + per : n4;
+    constexpr size_t TILE = (size_t)UNROLL * kThreads;
+    for (size_t t0 = lo + (size_t)blockIdx.x * TILE; t0 < hi; t0 += (size_t)gridDim.x * TILE) {
+        float4 in[UNROLL][NR];
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            const size_t v = t0 + (size_t)j * kThreads + threadIdx.x;
+            if (v < hi) {
+#pragma unroll
+                for (int p = 0; p < NR; ++p) in[j][p] = ld_f4<STRONG>(peers.data[p] + 4 * v);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            const size_t v = t0 + (size_t)j * kThreads + threadIdx.x;
+            if (v < hi) {
+                float4 s = in[j][0];
+#pragma unroll
+                for (int p = 1; p < NR; ++p) {
+                    s.x += in[j][p].x; s.y += in[j][p].y; s.z += in[j][p].z; s.w += in[j][p].w;
+                }
+#pragma unroll
+                for (int p = 0; p < NR; ++p) st_f4<STRONG>(peers.data[p] + 4 * v, s);
+            }
+        }
+    }
+    if (!gpu_barrier(mc_flag, uc_flag, epoch + 2u * (unsigned)NR, timeout_ns)) {
+        if (threadIdx.x == 0) atomicExch(err, 2);
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------------------
 
 struct NvlsRank {
@@ -281,7 +365,11 @@ int build_team(NvlsTeam &t, int ndev, const int *devs, size_t data_bytes, int it
         B200V_CU(d.MemAddressReserve(&r.uc, t.size, gran, 0, 0));
         B200V_CU(d.MemMap(r.uc, t.size, 0, r.mem, 0));
         r.uc_mapped = true;
-        B200V_CU(d.MemSetAccess(r.uc, t.size, &acc, 1));
+        // every GPU of the team may load from and store to this GPU's buffer (the peer-to-peer
+        // kernel does; the multicast kernel only touches its own)
+        std::vector<CUmemAccessDesc> all((size_t)ndev, acc);
+        for (int j = 0; j < ndev; ++j) all[(size_t)j].location.id = t.ranks[(size_t)j].cudev;
+        B200V_CU(d.MemSetAccess(r.uc, t.size, all.data(), (size_t)ndev));
         B200V_CU(d.MemAddressReserve(&r.mc, t.size, gran, 0, 0));
         B200V_CU(d.MemMap(r.mc, t.size, 0, t.mc_handle, 0));
         r.mc_mapped = true;
@@ -346,14 +434,38 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
     }
 
     unsigned epoch = 0;   // every launch consumes 2*ndev counts of each flag word
+    // Algorithm: switch-side reduction (multimem) from 4 GPUs up; with 2 GPUs there is nothing for
+    // the switch to reduce and the plain peer-to-peer form wins.  B200V_NVLS_ALGO=multimem|p2p
+    // overrides (p2p is compiled for 2, 4 and 8 GPUs).
+    // Measured busBW at 1 GiB (GB/s): 2 GPUs p2p 683 / multimem 394; 4 GPUs p2p 661 / multimem 678.
+    bool use_p2p = ndev == 2;
+    if (const char *e = std::getenv("B200V_NVLS_ALGO")) {
+        if (!std::strcmp(e, "p2p")) use_p2p = ndev == 2 || ndev == 4 || ndev == 8;
+        else if (!std::strcmp(e, "multimem")) use_p2p = false;
+    }
+    PeerPtrs peers;
+    std::memset(&peers, 0, sizeof peers);
+    for (int i = 0; i < ndev && i < kMaxPeers; ++i)
+        peers.data[i] = reinterpret_cast<float *>((unsigned char *)team.ranks[(size_t)i].uc + kFlagBytes);
+    if (use_p2p && !std::getenv("B200V_NVLS_CTAS")) ctas = std::min(team.ranks[0].sm_count, 64);
+
     auto allreduce_all = [&](size_t n4) -> int {
         for (int i = 0; i < ndev; ++i) {
             NvlsRank &r = team.ranks[(size_t)i];
             B200V_CUDA(cudaSetDevice(r.dev));
-            auto kern = unroll == 1 ? nvls_allreduce_kernel<1> : unroll == 2 ? nvls_allreduce_kernel<2>
-                      : unroll == 8 ? nvls_allreduce_kernel<8> : nvls_allreduce_kernel<4>;
-            kern<<<ctas, kThreads, 0, r.st>>>((unsigned char *)r.mc, (unsigned char *)r.uc, n4, i, ndev, epoch,
-                                              timeout_ns, r.d_err);
+            if (use_p2p) {
+                // Measured at 2 GPUs: weak vs .relaxed.sys accesses and twice the loads in flight all
+                // land on the same 680-686 GB/s — the link is the limit — so one shape per rank count.
+                auto kern = ndev == 2 ? p2p_allreduce_kernel<2, 4, true>
+                          : ndev == 4 ? p2p_allreduce_kernel<4, 2, true> : p2p_allreduce_kernel<8, 1, true>;
+                kern<<<ctas, kThreads, 0, r.st>>>(peers, (unsigned char *)r.mc, (unsigned char *)r.uc, n4, i, epoch,
+                                                  timeout_ns, r.d_err);
+            } else {
+                auto kern = unroll == 1 ? nvls_allreduce_kernel<1> : unroll == 2 ? nvls_allreduce_kernel<2>
+                          : unroll == 8 ? nvls_allreduce_kernel<8> : nvls_allreduce_kernel<4>;
+                kern<<<ctas, kThreads, 0, r.st>>>((unsigned char *)r.mc, (unsigned char *)r.uc, n4, i, ndev, epoch,
+                                                  timeout_ns, r.d_err);
+            }
             B200V_CUDA(cudaGetLastError());
         }
         epoch += 2u * (unsigned)ndev;
