@@ -87,8 +87,8 @@ func parseConfig() (*config, error) {
 	c.injectFault = int64(envInt("B200V_INJECT_FAULT", -1))
 	c.nvidiaSmi = envOr("B200V_NVIDIA_SMI", "nvidia-smi")
 	c.driverRoot = envOr("DRIVER_ROOT", "/run/nvidia/driver")
-	if c.mode != "validate" && c.mode != "stream" && c.mode != "nccl" {
-		return nil, fmt.Errorf("B200V_MODE must be validate, stream or nccl, not %s", c.mode)
+	if c.mode != "validate" && c.mode != "stream" && c.mode != "nccl" && c.mode != "nvls" {
+		return nil, fmt.Errorf("B200V_MODE must be validate, stream, nccl or nvls, not %s", c.mode)
 	}
 	return c, nil
 }
@@ -445,11 +445,19 @@ func runNcclProbe(c *config) int {
 	}
 	rows := make([]C.b200v_ar_row, 64)
 	var nrows C.int
-	rc := C.b200v_allreduce_probe(C.int(use), &devs[0], C.size_t(1)<<uint(envInt("B200V_MIN_LOG2", 10)),
-		C.size_t(1)<<uint(envInt("B200V_MAX_LOG2", 30)), 5, 20, &rows[0], 64, &nrows)
+	lo, hi := C.size_t(1)<<uint(envInt("B200V_MIN_LOG2", 10)), C.size_t(1)<<uint(envInt("B200V_MAX_LOG2", 30))
+	var rc C.int
+	if c.mode == "nvls" { // the hand-written NVLink kernels: same sweep, sizes multiple of 16 bytes
+		if lo < 16 {
+			lo = 16
+		}
+		rc = C.b200v_nvls_allreduce_probe(C.int(use), &devs[0], lo, hi, 5, 20, &rows[0], 64, &nrows)
+	} else {
+		rc = C.b200v_allreduce_probe(C.int(use), &devs[0], lo, hi, 5, 20, &rows[0], 64, &nrows)
+	}
 	failures := 0
 	if rc != 0 {
-		fmt.Fprintf(os.Stderr, "nccl probe failed: %s\n", strerror(rc))
+		fmt.Fprintf(os.Stderr, "%s probe failed: %s\n", c.mode, strerror(rc))
 		failures++
 	}
 	for i := 0; i < int(nrows); i++ {
@@ -457,8 +465,8 @@ func runNcclProbe(c *config) int {
 		if r.mismatches != 0 {
 			failures++
 		}
-		fmt.Printf("{\"mode\":\"nccl\",\"ranks\":%d,\"bytes\":%d,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%d}\n",
-			use, uint64(r.bytes), float64(r.busbw_gbs), float64(r.busbw_gbs)/900.0, uint64(r.mismatches))
+		fmt.Printf("{\"mode\":\"%s\",\"ranks\":%d,\"bytes\":%d,\"busbw_gbs\":%.2f,\"frac_of_900\":%.4f,\"mismatches\":%d}\n",
+			c.mode, use, uint64(r.bytes), float64(r.busbw_gbs), float64(r.busbw_gbs)/900.0, uint64(r.mismatches))
 	}
 	if failures > 0 {
 		return 1
@@ -475,7 +483,7 @@ func main() {
 	switch c.mode {
 	case "stream":
 		os.Exit(runStreamSweep(c))
-	case "nccl":
+	case "nccl", "nvls":
 		os.Exit(runNcclProbe(c))
 	}
 	if c.component == "" {
