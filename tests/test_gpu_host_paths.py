@@ -32,6 +32,36 @@ def test_ring_is_reused_and_regrown_across_calls(capi, oracle, gpu):
         assert t.kernel_launches == t.chunks >= 1
 
 
+def test_repeated_calls_do_not_leak_device_memory(capi, gpu):
+    """Entry points that allocate per call (stream rows, digest, check, the probes) give it all
+    back; the host path keeps only its bounded slot ring."""
+    import torch
+    n = (1 << 20) + 3
+    x = torch.rand(n, device="cuda")
+    a = np.ones(n, np.float32)
+    c = np.zeros(n, np.float32)
+
+    def one_round():
+        capi.stream(capi.OP_TRIAD, n, warmup=1, iters=2)
+        capi.digest_device(x.data_ptr(), n)
+        capi.check_device(capi.OP_COPY, x.data_ptr(), x.data_ptr(), None, 0.0, n)
+        capi.allreduce_probe([0], min_bytes=1 << 10, max_bytes=1 << 12, warmup=1, iters=2)
+        capi.vectoradd(a, a, c)
+        m = capi.NOALLOC_MAX_ELEMS
+        capi.vectoradd_noalloc(a[:m], a[:m], c[:m])
+
+    for _ in range(3):
+        one_round()                                   # warm: ring, staging, NCCL, lazy module loads
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(0)
+    for _ in range(25):
+        one_round()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(0)
+    # a leaked per-call buffer would cost >= 100 MiB here; allow NCCL's own small internal growth
+    assert free0 - free1 < (64 << 20), "device memory shrank by %d bytes over 25 rounds" % (free0 - free1)
+
+
 def test_concurrent_calls_from_threads(capi, oracle, gpu):
     """Two threads per visible GPU call b200v_vectoradd at once: calls on one device serialise on
     the library's per-device lock, calls on different devices run in parallel; all are exact."""
