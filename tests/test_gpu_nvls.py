@@ -23,6 +23,28 @@ def test_nvls_allreduce_probe_bit_exact(capi, gpu):
     assert top.busbw_gbs > 50.0
 
 
+def test_nvls_allreduce_ragged_slices_and_both_algorithms(capi, gpu, monkeypatch):
+    """Sizes whose float4 count is not a multiple of the rank count (63 * 2^k vectors), so the last
+    GPU's slice is short or empty, on the multimem kernel and on the peer-to-peer kernel."""
+    if gpu < 2:
+        pytest.skip("needs at least two GPUs")
+    ranks = 2 if gpu < 4 else (4 if gpu < 8 else 8)
+    for algo in ("multimem", "p2p"):
+        monkeypatch.setenv("B200V_NVLS_ALGO", algo)
+        try:
+            rows = capi.nvls_allreduce_probe(list(range(ranks)), min_bytes=63 * 16, max_bytes=63 * 16 << 12,
+                                             warmup=1, iters=3)
+        except capi.B200VError as e:
+            if e.code == capi.E_UNSUPPORTED:
+                pytest.skip("no multicast support on this box")
+            raise
+        assert [r.bytes for r in rows] == [63 * 16 << k for k in range(13)]
+        assert all(r.mismatches == 0 for r in rows), algo
+    # a tiny message: fewer vectors than ranks, most slices empty
+    rows = capi.nvls_allreduce_probe(list(range(ranks)), min_bytes=16, max_bytes=64, warmup=1, iters=2)
+    assert [r.bytes for r in rows] == [16, 32, 64] and all(r.mismatches == 0 for r in rows)
+
+
 def test_nvls_probe_argument_checks(capi, gpu):
     with pytest.raises(capi.B200VError) as ei:
         capi.nvls_allreduce_probe([0], min_bytes=1024, max_bytes=2048)
