@@ -480,6 +480,14 @@ func main() {
 		fmt.Fprintf(os.Stderr, "Incorrect Usage. %v\n", err)
 		os.Exit(1)
 	}
+	if c.mode != "validate" { // a probe that never completes must not hang the node's validation
+		if limit := envInt("B200V_PROBE_TIMEOUT_S", 600); limit > 0 {
+			time.AfterFunc(time.Duration(limit)*time.Second, func() {
+				fmt.Fprintln(os.Stderr, "probe timed out (B200V_PROBE_TIMEOUT_S)")
+				os.Exit(1)
+			})
+		}
+	}
 	switch c.mode {
 	case "stream":
 		os.Exit(runStreamSweep(c))

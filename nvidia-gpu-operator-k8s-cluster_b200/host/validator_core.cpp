@@ -7,6 +7,7 @@
 #include <cerrno>
 #include <cinttypes>
 #include <cmath>
+#include <csignal>
 #include <cstdlib>
 #include <cstring>
 #include <dirent.h>
@@ -685,6 +686,21 @@ int validator_main(const Api &api, int argc, char **argv) {
     if (!parse_config(argc, argv, cfg)) {
         std::fprintf(stderr, "Incorrect Usage. %s\n", cfg.error.c_str());
         return 1;
+    }
+    if (cfg.mode != "validate") {
+        // A health probe must not hang the node's validation: a collective that never completes
+        // (a wedged link, a bad NCCL_* override) ends the process with exit code 1 after
+        // B200V_PROBE_TIMEOUT_S seconds (default 600).
+        const int limit = env_int("B200V_PROBE_TIMEOUT_S", 600);
+        if (limit > 0) {
+            ::signal(SIGALRM, [](int) {
+                static const char msg[] = "probe timed out (B200V_PROBE_TIMEOUT_S)\n";
+                ssize_t ignored = ::write(2, msg, sizeof msg - 1);
+                (void)ignored;
+                ::_exit(1);
+            });
+            ::alarm((unsigned)limit);
+        }
     }
     if (cfg.mode == "stream") return run_stream_sweep(api, cfg, stdout, stderr);
     if (cfg.mode == "nccl" || cfg.mode == "nvls") return run_nccl_probe(api, cfg, stdout, stderr);

@@ -10,6 +10,7 @@
 //   FAKE_FAIL_DEVICE device the failure mode applies to (-1 = all, default)
 #include <cstdlib>
 #include <cstring>
+#include <unistd.h>
 
 #include "validator_core.h"
 
@@ -73,6 +74,7 @@ int fake_stream(int, int op, size_t n, float, uint64_t, int, int iters, b200v_st
 int fake_allreduce(int ndev, const int *, size_t lo, size_t hi, int, int, b200v_ar_row *rows, int max_rows,
                    int *nrows) {
     if (!std::strcmp(mode(), "cudaerr")) return B200V_E_NCCL;
+    if (!std::strcmp(mode(), "hang")) for (;;) ::pause();     // a collective that never completes
     int k = 0;
     for (size_t b = lo; b <= hi && k < max_rows; b *= 2) {
         std::memset(&rows[k], 0, sizeof rows[k]);

@@ -70,6 +70,13 @@ def test_with_workload_false_only_writes_the_status_file(fake, tmp_path):
     assert ready(tmp_path) == ["cuda-ready"]
 
 
+def test_probe_that_never_completes_is_cut_off(fake, tmp_path):
+    import time
+    t0 = time.time()
+    rc, _out, err = run(fake, tmp_path, B200V_MODE="nccl", FAKE_NDEV=8, FAKE_MODE="hang", B200V_PROBE_TIMEOUT_S=1)
+    assert rc == 1 and "probe timed out" in err and time.time() - t0 < 20
+
+
 def test_cuda_error_from_library_is_reported(fake, tmp_path):
     rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_MODE="cudaerr")
     assert rc == 1 and "illegal memory access" in err
