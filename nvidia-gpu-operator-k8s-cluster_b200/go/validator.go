@@ -376,12 +376,15 @@ func renderMetrics(c *config) string {
 	var b strings.Builder
 	for _, comp := range []string{"driver", "toolkit", "cuda", "plugin"} {
 		name := "gpu_operator_node_" + comp + "_ready"
-		v := 0
-		if _, err := os.Stat(statusPath(c, comp+"-ready")); err == nil {
-			v = 1
+		v, ts := 0, int64(0)
+		if fi, err := os.Stat(statusPath(c, comp+"-ready")); err == nil {
+			v, ts = 1, fi.ModTime().Unix()
 		}
 		fmt.Fprintf(&b, "# HELP %s 1 when %s validation has left its status file on this node\n# TYPE %s gauge\n%s %d\n",
 			name, comp, name, name, v)
+		tsName := "gpu_operator_node_" + comp + "_validation_last_success_ts_seconds"
+		fmt.Fprintf(&b, "# HELP %s unix time of the last successful %s validation (0 = never)\n# TYPE %s gauge\n%s %d\n",
+			tsName, comp, tsName, tsName, ts)
 	}
 	perGPU, _ := filepath.Glob(statusPath(c, "cuda-gpu*-ready"))
 	b.WriteString("# HELP b200v_node_cuda_gpu_ready 1 for every GPU whose own vectorAdd validation passed\n# TYPE b200v_node_cuda_gpu_ready gauge\n")

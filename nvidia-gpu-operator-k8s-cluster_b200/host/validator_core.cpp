@@ -465,6 +465,11 @@ std::string render_metrics(const Config &cfg) {
         m += "# HELP " + name + " 1 when " + c + " validation has left its status file on this node\n";
         m += "# TYPE " + name + " gauge\n";
         m += name + (ready ? " 1\n" : " 0\n");
+        // when it last succeeded = when its status file was (re)created
+        const std::string ts = std::string("gpu_operator_node_") + c + "_validation_last_success_ts_seconds";
+        m += "# HELP " + ts + " unix time of the last successful " + c + " validation (0 = never)\n";
+        m += "# TYPE " + ts + " gauge\n";
+        m += ts + " " + std::to_string(ready ? (long long)st.st_mtime : 0LL) + "\n";
     }
     // per-GPU fan-out files and bandwidth results
     std::vector<std::string> gpu_lines, prom_files;

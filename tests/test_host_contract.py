@@ -237,6 +237,11 @@ def test_metrics_oneshot_reflects_status_files_and_bandwidth(fake, tmp_path):
     lines = out.splitlines()
     assert "gpu_operator_node_cuda_ready 1" in lines and "gpu_operator_node_toolkit_ready 1" in lines
     assert "gpu_operator_node_driver_ready 0" in lines and "gpu_operator_node_plugin_ready 0" in lines
+    import time
+    ts = {l.split()[0]: int(l.split()[1]) for l in lines
+          if "_validation_last_success_ts_seconds " in l and not l.startswith("#")}
+    assert ts["gpu_operator_node_driver_validation_last_success_ts_seconds"] == 0
+    assert abs(ts["gpu_operator_node_cuda_validation_last_success_ts_seconds"] - time.time()) < 300
     assert 'b200v_node_cuda_gpu_ready{gpu="0"} 1' in lines and 'b200v_node_cuda_gpu_ready{gpu="1"} 1' in lines
     assert "gpu_operator_node_device_plugin_devices_total 2" in lines
     assert any(l.startswith('b200v_hbm_bandwidth_gbs{gpu="0",op="triad",log2_n="28"} ') for l in lines)
