@@ -363,27 +363,38 @@ def main():
                      "busbw_gbs_at_1GiB": top["busbw_gbs"], "frac_of_900": round(top["busbw_gbs"] / 900.0, 4),
                      "bit_exact": all(t["mismatches"] == 0 for t in table), "rows": table}
 
-    # ---- hand-written NVLink-multicast all-reduce (single process drives all GPUs) ---------------
-    # Rank 0 runs it over every GPU of the job while the other ranks wait on the HOST (a gloo
-    # barrier): they must not wait inside a GPU kernel, which would share the GPUs with the probe.
+    # ---- hand-written NVLink-multicast all-reduce, one process per GPU like everything else here --
+    # Every rank drives its own GPU; rank 0 hands the multicast object to the others over a Unix
+    # socket (csrc/rendezvous.h).  Times are per rank on the device; the job's time is the max.
     nvls = None
     if world > 1 and not args.no_allreduce:
         torch.cuda.synchronize()
-        host_group = dist.new_group(backend="gloo")
-        dist.barrier(group=host_group)
-        if rank == 0:
-            try:
-                vrows = capi.nvls_allreduce_probe(list(range(world)), min_bytes=1 << 20, max_bytes=1 << 30,
-                                                  warmup=5, iters=20)
-                vt = [{"bytes": int(r.bytes), "ms": round(r.best_ms, 4), "algbw_gbs": round(r.algbw_gbs, 1),
-                       "busbw_gbs": round(r.busbw_gbs, 1), "mismatches": int(r.mismatches)} for r in vrows]
-                nvls = {"op": "multimem.ld_reduce + multimem.st kernel, fp32 sum in place, one process",
-                        "busbw_gbs_at_1GiB": vt[-1]["busbw_gbs"], "frac_of_900": round(vt[-1]["busbw_gbs"] / 900.0, 4),
-                        "bit_exact": all(t["mismatches"] == 0 for t in vt), "gpu_launches": world * len(vt) * 26,
-                        "rows": vt}
-            except capi.B200VError as e:
-                nvls = {"unavailable": str(e)}
-        dist.barrier(group=host_group)
+        name = "b200v-nvls-%s-%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
+        try:
+            vrows = capi.nvls_allreduce_probe_rank(dev, rank, world, name, min_bytes=1 << 20, max_bytes=1 << 30,
+                                                   warmup=5, iters=20)
+            fail = 0.0
+        except capi.B200VError as e:
+            vrows, fail, why = [], 1.0, str(e)
+        failed = torch.tensor([fail], dtype=torch.float64, device="cuda")
+        dist.all_reduce(failed, op=dist.ReduceOp.MAX)
+        if failed.item() > 0:
+            nvls = {"unavailable": why if fail else "another rank failed"}
+        else:
+            vms = torch.tensor([r.best_ms for r in vrows], dtype=torch.float64, device="cuda")
+            vbad = torch.tensor([float(r.mismatches) for r in vrows], dtype=torch.float64, device="cuda")
+            dist.all_reduce(vms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(vbad, op=dist.ReduceOp.SUM)
+            vt = []
+            for r, t_ms, b in zip(vrows, vms.tolist(), vbad.tolist()):
+                alg = r.bytes / (t_ms * 1e-3) / 1e9
+                vt.append({"bytes": int(r.bytes), "ms": round(t_ms, 4), "algbw_gbs": round(alg, 1),
+                           "busbw_gbs": round(alg * 2 * (world - 1) / world, 1), "mismatches": int(b)})
+            nvls = {"op": ("peer load/store kernel" if world == 2 else "multimem.ld_reduce + multimem.st kernel")
+                    + ", fp32 sum in place, one process per GPU",
+                    "busbw_gbs_at_1GiB": vt[-1]["busbw_gbs"], "frac_of_900": round(vt[-1]["busbw_gbs"] / 900.0, 4),
+                    "bit_exact": all(t["mismatches"] == 0 for t in vt), "gpu_launches": world * len(vt) * 26,
+                    "rows": vt}
 
     # ---- CPU baseline: the sample's host verification loop, one thread, rank 0 at N=1 -------------
     cpu = None

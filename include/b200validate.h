@@ -229,6 +229,16 @@ int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size
                                int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
 int b200v_last_driver_error(void);
 
+/* One-process-per-GPU form of the same probe.  Every rank calls it with the same `rendezvous`
+ * string — the name of an abstract-namespace Unix socket on which rank 0 hands the multicast
+ * object's file descriptor to the other ranks of this host (and, for the 2-rank peer-to-peer
+ * kernel, relays every rank's buffer descriptor to every other rank).  Collective; the
+ * times are this rank's and the caller takes the max over ranks, as with
+ * b200v_allreduce_probe_rank.  A rank that never shows up yields B200V_E_TIMEOUT after 60 s. */
+int b200v_nvls_allreduce_probe_rank(int dev, int rank, int nranks, const char *rendezvous,
+                                    size_t min_bytes, size_t max_bytes, int warmup, int iters,
+                                    b200v_ar_row *rows, int max_rows, int *nrows);
+
 /* Releases cached per-device state (streams, events, staging buffers). */
 int b200v_shutdown(void);
 

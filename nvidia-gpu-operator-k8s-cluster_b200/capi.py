@@ -85,6 +85,7 @@ SIGNATURES = {
     "b200v_last_nccl_error": (_i, []),
     "b200v_nvls_allreduce_probe": (_i, [_i, _P(_i), _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_last_driver_error": (_i, []),
+    "b200v_nvls_allreduce_probe_rank": (_i, [_i, _i, _i, ctypes.c_char_p, _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_shutdown": (_i, []),
 }
 
@@ -278,6 +279,17 @@ def nvls_allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iter
     n = _i()
     _check(lib().b200v_nvls_allreduce_probe(len(devs), arr, min_bytes, max_bytes, warmup, iters, rows, 64,
                                             ctypes.byref(n)), "b200v_nvls_allreduce_probe")
+    return _rows(rows, n.value)
+
+
+def nvls_allreduce_probe_rank(dev, rank, nranks, rendezvous, min_bytes=1024, max_bytes=1 << 30, warmup=5,
+                              iters=20):
+    """One rank of the hand-written all-reduce probe, one process per GPU (collective call)."""
+    rows = (ArRow * 64)()
+    n = _i()
+    _check(lib().b200v_nvls_allreduce_probe_rank(dev, rank, nranks, rendezvous.encode(), min_bytes, max_bytes,
+                                                 warmup, iters, rows, 64, ctypes.byref(n)),
+           "b200v_nvls_allreduce_probe_rank")
     return _rows(rows, n.value)
 
 

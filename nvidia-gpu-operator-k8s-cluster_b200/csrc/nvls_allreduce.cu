@@ -20,14 +20,22 @@
 // keeps having no link-time dependency on libcuda.  The spin loops are bounded (B200V_NVLS_TIMEOUT_MS,
 // default 2000): a peer that never arrives yields B200V_E_TIMEOUT, never a hung GPU.
 #include <algorithm>
+#include <cstddef>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <cuda.h>   // types and enums; every driver function is fetched at run time
+#include <poll.h>
+#include <sys/socket.h>
+#include <sys/uio.h>
+#include <sys/un.h>
+#include <unistd.h>
 #include <vector>
 
 #include "ar_common.cuh"
 #include "common.cuh"
+#include "rendezvous.h"
 
 namespace b200v {
 namespace {
@@ -255,6 +263,7 @@ p2p_allreduce_kernel(PeerPtrs peers, unsigned char *mc_base, unsigned char *uc_b
 
 struct NvlsRank {
     int dev = -1;
+    int rank = -1;          // rank in the collective
     CUdevice cudev = 0;
     CUmemGenericAllocationHandle mem = 0;
     CUdeviceptr uc = 0, mc = 0;
@@ -271,6 +280,12 @@ struct NvlsTeam {
     CUmemGenericAllocationHandle mc_handle = 0;
     size_t size = 0;
     bool have_mc = false;
+    // Address of every rank's buffer as seen from this process (index = rank), for the
+    // peer-to-peer kernel.  One process: the ranks' own mappings.  One process per GPU: the other
+    // ranks' allocations imported (peer_mem) and mapped here (peer_va).  Empty when unavailable.
+    std::vector<CUdeviceptr> peer_uc;
+    std::vector<CUmemGenericAllocationHandle> peer_mem;
+    std::vector<CUdeviceptr> peer_va;
 };
 
 #define B200V_CU(expr)                                   \
@@ -278,6 +293,8 @@ struct NvlsTeam {
         CUresult r__ = (expr);                           \
         if (r__ != CUDA_SUCCESS) {                       \
             g_last_cu = (int)r__;                        \
+            std::fprintf(stderr, "b200v: CUDA driver call failed with CUresult %d at %s:%d: %s\n", (int)r__, \
+                         "nvls_allreduce.cu", __LINE__, #expr);                                             \
             return r__ == CUDA_ERROR_NOT_SUPPORTED ? B200V_E_UNSUPPORTED : B200V_E_DRIVER; \
         }                                                \
     } while (0)
@@ -291,6 +308,14 @@ void destroy_team(NvlsTeam &t) {
         cudaSetDevice(r.dev);
         if (r.st) cudaStreamSynchronize(r.st);
     }
+    for (CUdeviceptr va : t.peer_va) {
+        d.MemUnmap(va, t.size);
+        d.MemAddressFree(va, t.size);
+    }
+    for (CUmemGenericAllocationHandle h : t.peer_mem) d.MemRelease(h);
+    t.peer_va.clear();
+    t.peer_mem.clear();
+    t.peer_uc.clear();
     for (NvlsRank &r : t.ranks) {
         if (r.dev < 0) continue;
         cudaSetDevice(r.dev);
@@ -316,6 +341,7 @@ int build_team(NvlsTeam &t, int ndev, const int *devs, size_t data_bytes, int it
     for (int i = 0; i < ndev; ++i) {
         NvlsRank &r = t.ranks[(size_t)i];
         r.dev = devs[i];
+        r.rank = i;
         B200V_CUDA(cudaSetDevice(r.dev));
         B200V_CUDA(cudaFree(nullptr));   // make sure the primary context exists
         B200V_CU(d.DeviceGet(&r.cudev, r.dev));
@@ -377,6 +403,133 @@ int build_team(NvlsTeam &t, int ndev, const int *devs, size_t data_bytes, int it
         B200V_CUDA(cudaMemsetAsync((void *)r.uc, 0, kFlagBytes, r.st));
         B200V_CUDA(cudaStreamSynchronize(r.st));
     }
+    for (NvlsRank &r : t.ranks) t.peer_uc.push_back(r.uc);
+    return B200V_OK;
+}
+
+// ---- one process per GPU (see rendezvous.h for how the processes meet) --------------------------------
+// This process's one rank of an nranks-wide team whose other ranks live in other processes.
+int build_team_rank(NvlsTeam &t, Rendezvous &rv, int dev, int rank, int nranks, size_t data_bytes, int iters) {
+    const Drv &d = drv();
+    CUresult (*Export)(void *, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
+    CUresult (*Import)(CUmemGenericAllocationHandle *, void *, CUmemAllocationHandleType) = nullptr;
+    if (!d.ok || !drv_sym("cuMemExportToShareableHandle", Export) || !drv_sym("cuMemImportFromShareableHandle", Import))
+        return B200V_E_UNSUPPORTED;
+    t.ranks.resize(1);
+    NvlsRank &r = t.ranks[0];
+    r.dev = dev;
+    r.rank = rank;
+    B200V_CUDA(cudaSetDevice(r.dev));
+    B200V_CUDA(cudaFree(nullptr));
+    B200V_CU(d.DeviceGet(&r.cudev, r.dev));
+    int mc_ok = 0;
+    B200V_CU(d.DeviceGetAttribute(&mc_ok, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, r.cudev));
+    if (!mc_ok) return B200V_E_UNSUPPORTED;
+    B200V_CUDA(cudaDeviceGetAttribute(&r.sm_count, cudaDevAttrMultiProcessorCount, r.dev));
+    B200V_CUDA(cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+    B200V_CUDA(cudaMalloc(&r.d_bad, 8));
+    B200V_CUDA(cudaMalloc(&r.d_err, 4));
+    B200V_CUDA(cudaMemset(r.d_err, 0, 4));
+    r.ev.resize((size_t)iters * 2);
+    for (auto &e : r.ev) B200V_CUDA(cudaEventCreate(&e));
+
+    CUmulticastObjectProp mprop;
+    std::memset(&mprop, 0, sizeof mprop);
+    mprop.numDevices = (unsigned)nranks;
+    mprop.size = kFlagBytes + data_bytes;
+    mprop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t gran = 0;
+    B200V_CU(d.MulticastGetGranularity(&gran, &mprop, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+    CUmemAllocationProp aprop;
+    std::memset(&aprop, 0, sizeof aprop);
+    aprop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    aprop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    aprop.location.id = r.cudev;
+    aprop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;   // same kind as the multicast object
+    size_t agran = 0;
+    B200V_CU(d.MemGetAllocationGranularity(&agran, &aprop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+    gran = std::max(gran, agran);
+    t.size = (mprop.size + gran - 1) / gran * gran;     // every rank computes the same size
+    mprop.size = t.size;
+
+    int fd = -1;
+    if (rank == 0) {
+        B200V_CU(d.MulticastCreate(&t.mc_handle, &mprop));
+        t.have_mc = true;
+        B200V_CU(Export(&fd, t.mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+    }
+    const bool shared = rv.share_fd(fd);
+    if (rank == 0) {
+        if (fd >= 0) ::close(fd);
+    } else if (shared) {
+        CUresult ir = Import(&t.mc_handle, (void *)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+        ::close(fd);
+        B200V_CU(ir);
+        t.have_mc = true;
+    }
+    if (!shared) return B200V_E_TIMEOUT;
+    B200V_CU(d.MulticastAddDevice(t.mc_handle, r.cudev));
+    if (!rv.barrier()) return B200V_E_TIMEOUT;          // every device is in the team before anyone binds
+
+    B200V_CU(d.MemCreate(&r.mem, t.size, &aprop, 0));
+    B200V_CU(d.MulticastBindMem(t.mc_handle, 0, r.mem, 0, t.size, 0));
+    r.bound = true;
+    CUmemAccessDesc acc;
+    std::memset(&acc, 0, sizeof acc);
+    acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    acc.location.id = r.cudev;
+    acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    B200V_CU(d.MemAddressReserve(&r.uc, t.size, gran, 0, 0));
+    B200V_CU(d.MemMap(r.uc, t.size, 0, r.mem, 0));
+    r.uc_mapped = true;
+    B200V_CU(d.MemSetAccess(r.uc, t.size, &acc, 1));
+    B200V_CU(d.MemAddressReserve(&r.mc, t.size, gran, 0, 0));
+    B200V_CU(d.MemMap(r.mc, t.size, 0, t.mc_handle, 0));
+    r.mc_mapped = true;
+    B200V_CU(d.MemSetAccess(r.mc, t.size, &acc, 1));
+    B200V_CUDA(cudaMemsetAsync((void *)r.uc, 0, kFlagBytes, r.st));
+    B200V_CUDA(cudaStreamSynchronize(r.st));
+
+    // For the peer-to-peer kernel (2 ranks, or forced) every rank also maps every other rank's
+    // buffer: each exports its allocation as a descriptor, rank 0 relays them all around.  All ranks
+    // take this branch or none (same nranks, same environment).
+    const char *algo = std::getenv("B200V_NVLS_ALGO");
+    const bool want_peers = algo ? !std::strcmp(algo, "p2p") && (nranks == 2 || nranks == 4 || nranks == 8)
+                                 : nranks == 2;
+    if (want_peers) {
+        int my_fd = -1;
+        B200V_CU(Export(&my_fd, r.mem, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+        std::vector<int> fds;
+        const bool ok = rv.exchange_fds(my_fd, fds);
+        int rc = ok ? B200V_OK : B200V_E_TIMEOUT;
+        std::vector<CUdeviceptr> uc((size_t)nranks, 0);
+        uc[(size_t)rank] = r.uc;
+        for (int k = 0; ok && k < nranks && rc == B200V_OK; ++k) {
+            if (k == rank) continue;
+            CUmemGenericAllocationHandle h = 0;
+            CUdeviceptr va = 0;
+            if (Import(&h, (void *)(uintptr_t)fds[(size_t)k], CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR) != CUDA_SUCCESS) {
+                rc = B200V_E_DRIVER;
+                break;
+            }
+            t.peer_mem.push_back(h);
+            if (d.MemAddressReserve(&va, t.size, gran, 0, 0) != CUDA_SUCCESS) { rc = B200V_E_DRIVER; break; }
+            if (d.MemMap(va, t.size, 0, h, 0) != CUDA_SUCCESS) {
+                d.MemAddressFree(va, t.size);
+                rc = B200V_E_DRIVER;
+                break;
+            }
+            t.peer_va.push_back(va);
+            if (d.MemSetAccess(va, t.size, &acc, 1) != CUDA_SUCCESS) { rc = B200V_E_DRIVER; break; }
+            uc[(size_t)k] = va;
+        }
+        for (int k = 0; k < (int)fds.size(); ++k)
+            if (fds[(size_t)k] >= 0) ::close(fds[(size_t)k]);      // includes my_fd (fds[rank])
+        if (fds.empty() && my_fd >= 0) ::close(my_fd);
+        if (rc != B200V_OK) return rc;
+        t.peer_uc = uc;
+    }
+    if (!rv.barrier()) return B200V_E_TIMEOUT;          // every flag word is zero before the first launch
     return B200V_OK;
 }
 
@@ -394,26 +547,15 @@ using namespace b200v;
 
 extern "C" int b200v_last_driver_error(void) { return g_last_cu; }
 
-extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
-                                          int warmup, int iters, b200v_ar_row *rows, int max_rows,
-                                          int *nrows) {
-    if (ndev < 2 || !devs || !rows || !nrows || max_rows < 1 || iters < 1 || warmup < 0 || min_bytes < 16 ||
-        (min_bytes & 15) || max_bytes < min_bytes)
-        return B200V_E_BADARG;
-    *nrows = 0;
-    int count = 0;
-    int rc = b200v_device_count(&count);
-    if (rc != B200V_OK) return rc;
-    for (int i = 0; i < ndev; ++i)
-        if (devs[i] < 0 || devs[i] >= count) return B200V_E_BADARG;
-
-    NvlsTeam team;
-    struct Cleanup {
-        NvlsTeam &t;
-        ~Cleanup() { destroy_team(t); }
-    } cleanup{team};
-    rc = build_team(team, ndev, devs, max_bytes, iters);
-    if (rc != B200V_OK) return rc;
+// The sweep over message sizes, for the ranks this process drives (all of them in the
+// single-process probe, one in the per-rank probe).  Every rank of the collective runs the same
+// sequence of launches, so the barrier epochs stay in step without any host-side exchange.
+static int sweep_team(NvlsTeam &team, int nranks, size_t min_bytes, size_t max_bytes, int warmup, int iters,
+                      b200v_ar_row *rows, int max_rows, int *nrows) {
+    const int ndev = nranks;
+    // every rank's buffer is addressable from here (one process, or imported peer mappings)
+    const bool all_local = (int)team.peer_uc.size() == nranks && nranks <= kMaxPeers;
+    int rc = B200V_OK;
 
     // Few CTAs are enough to keep the NVLink ports busy, and more only add barrier traffic and
     // switch-side contention: measured on 8 x B200 (busBW GB/s at 16 MiB / 64 MiB / 1 GiB)
@@ -438,20 +580,20 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
     // the switch to reduce and the plain peer-to-peer form wins.  B200V_NVLS_ALGO=multimem|p2p
     // overrides (p2p is compiled for 2, 4 and 8 GPUs).
     // Measured busBW at 1 GiB (GB/s): 2 GPUs p2p 683 / multimem 394; 4 GPUs p2p 661 / multimem 678.
-    bool use_p2p = ndev == 2;
+    bool use_p2p = ndev == 2 && all_local;
     if (const char *e = std::getenv("B200V_NVLS_ALGO")) {
-        if (!std::strcmp(e, "p2p")) use_p2p = ndev == 2 || ndev == 4 || ndev == 8;
+        if (!std::strcmp(e, "p2p")) use_p2p = all_local && (ndev == 2 || ndev == 4 || ndev == 8);
         else if (!std::strcmp(e, "multimem")) use_p2p = false;
     }
     PeerPtrs peers;
     std::memset(&peers, 0, sizeof peers);
-    for (int i = 0; i < ndev && i < kMaxPeers; ++i)
-        peers.data[i] = reinterpret_cast<float *>((unsigned char *)team.ranks[(size_t)i].uc + kFlagBytes);
+    for (int i = 0; all_local && i < ndev && i < kMaxPeers; ++i)
+        peers.data[i] = reinterpret_cast<float *>((unsigned char *)team.peer_uc[(size_t)i] + kFlagBytes);
     if (use_p2p && !std::getenv("B200V_NVLS_CTAS")) ctas = std::min(team.ranks[0].sm_count, 64);
 
     auto allreduce_all = [&](size_t n4) -> int {
-        for (int i = 0; i < ndev; ++i) {
-            NvlsRank &r = team.ranks[(size_t)i];
+        for (NvlsRank &r : team.ranks) {
+            const int i = r.rank;
             B200V_CUDA(cudaSetDevice(r.dev));
             if (use_p2p) {
                 // Measured at 2 GPUs: weak vs .relaxed.sys accesses and twice the loads in flight all
@@ -490,8 +632,8 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
         row->bytes = bytes;
         const size_t count_f = bytes / 4, n4 = bytes / 16;
 
-        for (int i = 0; i < ndev; ++i) {
-            NvlsRank &r = team.ranks[(size_t)i];
+        for (NvlsRank &r : team.ranks) {
+            const int i = r.rank;
             B200V_CUDA(cudaSetDevice(r.dev));
             float *data = reinterpret_cast<float *>((unsigned char *)r.uc + kFlagBytes);
             ar_fill_kernel<<<grid_fill(r, count_f), 256, 0, r.st>>>(data, count_f, i);
@@ -500,8 +642,8 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
         }
         rc = allreduce_all(n4);
         if (rc != B200V_OK) return rc;
-        for (int i = 0; i < ndev; ++i) {
-            NvlsRank &r = team.ranks[(size_t)i];
+        for (NvlsRank &r : team.ranks) {
+            const int i = r.rank;
             B200V_CUDA(cudaSetDevice(r.dev));
             const float *data = reinterpret_cast<const float *>((unsigned char *)r.uc + kFlagBytes);
             ar_check_kernel<<<grid_fill(r, count_f), 256, 0, r.st>>>(data, count_f, ndev, r.d_bad);
@@ -551,4 +693,62 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
     }
     *nrows = nr;
     return B200V_OK;
+}
+
+static bool bad_probe_args(size_t min_bytes, size_t max_bytes, int warmup, int iters, const void *rows,
+                           int max_rows, const int *nrows) {
+    return !rows || !nrows || max_rows < 1 || iters < 1 || warmup < 0 || min_bytes < 16 || (min_bytes & 15) ||
+           max_bytes < min_bytes;
+}
+
+extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
+                                          int warmup, int iters, b200v_ar_row *rows, int max_rows,
+                                          int *nrows) {
+    if (ndev < 2 || !devs || bad_probe_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
+        return B200V_E_BADARG;
+    *nrows = 0;
+    int count = 0;
+    int rc = b200v_device_count(&count);
+    if (rc != B200V_OK) return rc;
+    for (int i = 0; i < ndev; ++i)
+        if (devs[i] < 0 || devs[i] >= count) return B200V_E_BADARG;
+
+    NvlsTeam team;
+    struct Cleanup {
+        NvlsTeam &t;
+        ~Cleanup() { destroy_team(t); }
+    } cleanup{team};
+    rc = build_team(team, ndev, devs, max_bytes, iters);
+    if (rc != B200V_OK) return rc;
+    return sweep_team(team, ndev, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
+}
+
+extern "C" int b200v_nvls_allreduce_probe_rank(int dev, int rank, int nranks, const char *rendezvous,
+                                               size_t min_bytes, size_t max_bytes, int warmup, int iters,
+                                               b200v_ar_row *rows, int max_rows, int *nrows) {
+    if (nranks < 2 || rank < 0 || rank >= nranks || !rendezvous || !*rendezvous ||
+        bad_probe_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
+        return B200V_E_BADARG;
+    *nrows = 0;
+    int count = 0;
+    int rc = b200v_device_count(&count);
+    if (rc != B200V_OK) return rc;
+    if (dev < 0 || dev >= count) return B200V_E_BADARG;
+
+    Rendezvous rv;
+    NvlsTeam team;
+    struct Cleanup {
+        NvlsTeam &t;
+        Rendezvous &rv;
+        ~Cleanup() {
+            rv.barrier();        // nobody unbinds while a peer's kernel may still be running
+            destroy_team(t);
+            rv.close_all();
+        }
+    } cleanup{team, rv};
+    rc = rv.open(rendezvous, rank, nranks);
+    if (rc != B200V_OK) return rc;
+    rc = build_team_rank(team, rv, dev, rank, nranks, max_bytes, iters);
+    if (rc != B200V_OK) return rc;
+    return sweep_team(team, nranks, min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows);
 }
