@@ -409,10 +409,44 @@ func runStreamSweep(c *config) int {
 		name string
 	}{{C.B200V_OP_COPY, "copy"}, {C.B200V_OP_SCALE, "scale"}, {C.B200V_OP_ADD, "add"}, {C.B200V_OP_TRIAD, "triad"}}
 	failures := 0
+	if c.childDevice < 0 && c.gpus > 1 { // one sweep per device, each in its own process, all at once
+		self, _ := os.Executable()
+		var wg sync.WaitGroup
+		results := make([]int, c.gpus)
+		for i := 0; i < c.gpus; i++ {
+			wg.Add(1)
+			go func(i int) {
+				defer wg.Done()
+				cmd := exec.Command(self, "--mode", "stream")
+				cmd.Env = append(os.Environ(), "B200V_CHILD_DEVICE="+strconv.Itoa(i))
+				cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
+				if err := cmd.Run(); err != nil {
+					results[i] = 1
+				}
+			}(i)
+		}
+		wg.Wait()
+		for i, rc := range results {
+			if rc != 0 {
+				fmt.Fprintf(os.Stderr, "stream sweep failed on gpu %d (exit code %d)\n", i, rc)
+				failures++
+			}
+		}
+		if failures > 0 {
+			return 1
+		}
+		return 0
+	}
+	dev := 0
+	if c.childDevice >= 0 {
+		dev = c.childDevice
+	}
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
 	for lg := envInt("B200V_MIN_LOG2", 18); lg <= envInt("B200V_MAX_LOG2", 32); lg++ {
 		for _, op := range ops {
 			var r C.b200v_stream_result
-			rc := C.b200v_stream(0, op.id, C.size_t(1)<<uint(lg), 3.0, 0xB200, 5, 20, &r)
+			rc := C.b200v_stream(C.int(dev), op.id, C.size_t(1)<<uint(lg), 3.0, 0xB200, 5, 20, &r)
 			if rc != 0 && rc != C.B200V_E_MISMATCH {
 				fmt.Fprintf(os.Stderr, "stream %s n=2^%d failed: %s\n", op.name, lg, strerror(rc))
 				failures++
@@ -421,8 +455,8 @@ func runStreamSweep(c *config) int {
 			if r.mismatches != 0 {
 				failures++
 			}
-			fmt.Printf("{\"mode\":\"stream\",\"op\":\"%s\",\"log2_n\":%d,\"median_gbs\":%.1f,\"best_gbs\":%.1f,"+
-				"\"l2_resident\":%d,\"mismatches\":%d,\"digest\":\"%016x\"}\n", op.name, lg, float64(r.median_gbs),
+			fmt.Printf("{\"mode\":\"stream\",\"gpu\":%d,\"op\":\"%s\",\"log2_n\":%d,\"median_gbs\":%.1f,\"best_gbs\":%.1f,"+
+				"\"l2_resident\":%d,\"mismatches\":%d,\"digest\":\"%016x\"}\n", dev, op.name, lg, float64(r.median_gbs),
 				float64(r.best_gbs), int(r.l2_resident), uint64(r.mismatches), uint64(r.digest))
 		}
 	}

@@ -493,11 +493,26 @@ std::string render_metrics(const Config &cfg) {
     m += "# HELP gpu_operator_node_device_plugin_devices_total GPUs that passed cuda validation on this node\n";
     m += "# TYPE gpu_operator_node_device_plugin_devices_total gauge\n";
     m += "gpu_operator_node_device_plugin_devices_total " + std::to_string(gpu_lines.size()) + "\n";
+    // Several result files may describe the same metric family (one file per GPU): its HELP and
+    // TYPE lines go out once.
+    std::vector<std::string> seen_meta;
     for (const std::string &f : prom_files) {
         bool ok = false;
         const std::string text = read_file(status_path(cfg, f), ok);
-        if (ok) m += text;
-        if (ok && !text.empty() && text.back() != '\n') m += "\n";
+        if (!ok) continue;
+        size_t at = 0;
+        while (at < text.size()) {
+            size_t end = text.find('\n', at);
+            if (end == std::string::npos) end = text.size();
+            const std::string line = text.substr(at, end - at);
+            at = end + 1;
+            if (line.empty()) continue;
+            if (line.rfind("# HELP ", 0) == 0 || line.rfind("# TYPE ", 0) == 0) {
+                if (std::find(seen_meta.begin(), seen_meta.end(), line) != seen_meta.end()) continue;
+                seen_meta.push_back(line);
+            }
+            m += line + "\n";
+        }
     }
     return m;
 }
@@ -579,6 +594,23 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
         std::fprintf(err, "stream sweep failed: %s\n", api.strerror(rc != B200V_OK ? rc : B200V_E_NODEVICE));
         return 1;
     }
+    // B200V_GPUS > 1: one sweep per device, each in its own process, all at once — the per-GPU
+    // fan-out of the validation applied to the bandwidth sweep.  Each child prints
+    // its rows with its own "gpu" index; the sweep passes when every child does.
+    if (cfg.child_device < 0 && cfg.gpus > 1) {
+        if (cfg.gpus > ndev) {
+            std::fprintf(err, "stream sweep failed: B200V_GPUS=%d but only %d device(s) visible\n", cfg.gpus, ndev);
+            return 1;
+        }
+        std::vector<int> results = fan_out(cfg, cfg.gpus, {"--mode", "stream"});
+        int bad = 0;
+        for (int i = 0; i < cfg.gpus; ++i)
+            if (results[(size_t)i] != 0) {
+                std::fprintf(err, "stream sweep failed on gpu %d (exit code %d)\n", i, results[(size_t)i]);
+                ++bad;
+            }
+        return bad ? 1 : 0;
+    }
     const int dev = cfg.child_device >= 0 ? cfg.child_device : 0;
     const int lo = env_int("B200V_MIN_LOG2", 18), hi = env_int("B200V_MAX_LOG2", 32);
     const int ops[] = {B200V_OP_COPY, B200V_OP_SCALE, B200V_OP_ADD, B200V_OP_TRIAD};
@@ -617,7 +649,8 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
             }
         }
     }
-    write_prom(cfg, "hbm-bandwidth.prom", prom);
+    write_prom(cfg, cfg.child_device >= 0 ? "hbm-bandwidth-gpu" + std::to_string(dev) + ".prom" : "hbm-bandwidth.prom",
+               prom);
     return failures ? 1 : 0;
 }
 

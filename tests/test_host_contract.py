@@ -70,6 +70,24 @@ def test_with_workload_false_only_writes_the_status_file(fake, tmp_path):
     assert ready(tmp_path) == ["cuda-ready"]
 
 
+def test_stream_sweep_fans_out_per_gpu(fake, tmp_path):
+    rc, out, err = run(fake, tmp_path, B200V_MODE="stream", FAKE_NDEV=4, B200V_GPUS=4, B200V_MIN_LOG2=27,
+                       B200V_MAX_LOG2=27, B200V_WRITE_PROM=1)
+    assert rc == 0, err
+    rows = [json.loads(line) for line in out.splitlines()]
+    assert sorted(r["gpu"] for r in rows) == [g for g in range(4) for _ in range(4)]      # 4 ops per GPU
+    assert sorted(f for f in os.listdir(tmp_path) if f.endswith(".prom")) == [
+        "hbm-bandwidth-gpu%d.prom" % g for g in range(4)]
+    rc, metrics, _err = run(fake, tmp_path, COMPONENT="metrics", B200V_METRICS_ONESHOT=1)
+    assert metrics.count("# TYPE b200v_hbm_bandwidth_gbs gauge") == 1                       # one family header
+    assert metrics.count('b200v_hbm_bandwidth_gbs{gpu="') == 16
+    rc, _out, err = run(fake, tmp_path, B200V_MODE="stream", FAKE_NDEV=2, B200V_GPUS=4, B200V_MAX_LOG2=18)
+    assert rc == 1 and "only 2 device(s) visible" in err
+    rc, _out, err = run(fake, tmp_path, B200V_MODE="stream", FAKE_NDEV=2, B200V_GPUS=2, B200V_MAX_LOG2=18,
+                        FAKE_MODE="wrong")
+    assert rc == 1 and "stream sweep failed on gpu 0" in err and "stream sweep failed on gpu 1" in err
+
+
 def test_probe_that_never_completes_is_cut_off(fake, tmp_path):
     import time
     t0 = time.time()
