@@ -142,7 +142,14 @@ int b200v_vectoradd(int dev, const float *hA, const float *hB, float *hC, size_t
  *   - `stream` is the caller's cudaStream_t (NULL = default stream); the call enqueues two H2D
  *     copies, the kernel and one D2H copy on it and returns after synchronising it.
  *   - The first call on each GPU also performs that GPU's one-time set-up (looking up the
- *     array's device address); make it before starting any stream capture.
+ *     array's device address); make it before starting any stream capture.  CUDA loads modules
+ *     lazily, so that first call is also when the 12 MiB are reserved on the GPU (and when the
+ *     context is created, if the process had none): on a GPU that is already full it can fail
+ *     with cudaErrorMemoryAllocation.  Make it when the probe process starts, before the tenant
+ *     fills HBM (or start the process with CUDA_MODULE_LOADING=EAGER); later calls reserve
+ *     nothing.
+ *   - On a CUDA error after the first copy was enqueued the call waits for the stream before
+ *     returning, so the caller's host buffers are never still in use when it returns.
  *   - All calls on one GPU share the array, which still holds the previous call's data: calls
  *     that overlap in time on the same GPU race with each other, so serialise them.  No clearing
  *     is needed between calls (every element read was written earlier in the same call). */

@@ -7,8 +7,16 @@
 // cudaFree also synchronise the device, which stalls the tenant's streams for the duration.  The
 // regular entry point (b200v_vectoradd) allocates a ring of staging slots and creates streams and
 // events on first use; this one touches none of that.  Its device staging lives in the
-// file-scope array below, reserved when the library's module is loaded on a GPU and held until
-// the process exits, so the probe can always run and never asks the allocator for anything.
+// file-scope array below, which belongs to the library's CUDA module and is held until the
+// process exits, so once it is in place a probe never asks the allocator for anything.
+//
+// When the 12 MiB are actually taken: CUDA loads modules lazily by default (CUDA >= 12.2), so
+// the array is reserved on a GPU when this module is first used there — normally this entry
+// point's first call on that GPU (or at start-up with CUDA_MODULE_LOADING=EAGER).  That one
+// call also creates the CUDA context if the process has none yet.  On a GPU that is already
+// full it can therefore fail with cudaErrorMemoryAllocation like any allocation would.  Make the
+// first call on every GPU when the probe process starts, before the tenant fills HBM; every
+// later call finds the array in place and reserves nothing.
 //
 // What the caller gives up: the problem size is capped at B200V_NOALLOC_MAX_ELEMS elements per
 // vector (larger n is refused with B200V_E_TOOLARGE, nothing is computed), there is no
@@ -64,6 +72,18 @@ int scratch_for_device(int dev, float **out) {
         }                                                  \
     } while (0)
 
+// After the first copy has been enqueued an error must not return while the stream may still be
+// reading or writing the caller's host buffers: wait for whatever was enqueued, then report.
+#define NOALLOC_CUDA_DRAIN(expr, st)                       \
+    do {                                                   \
+        cudaError_t e__ = (expr);                          \
+        if (e__ != cudaSuccess) {                          \
+            (void)cudaStreamSynchronize(st);               \
+            (void)cudaGetLastError();                      \
+            return (int)e__;                               \
+        }                                                  \
+    } while (0)
+
 }  // namespace
 
 extern "C" int b200v_vectoradd_noalloc(int dev, const float *hA, const float *hB, float *hC, size_t n,
@@ -88,15 +108,15 @@ extern "C" int b200v_vectoradd_noalloc(int dev, const float *hA, const float *hB
     float *dB = base + (size_t)B200V_NOALLOC_MAX_ELEMS;
     float *dC = base + 2 * (size_t)B200V_NOALLOC_MAX_ELEMS;
     NOALLOC_CUDA(cudaMemcpyAsync(dA, hA, n * sizeof(float), cudaMemcpyHostToDevice, st));
-    NOALLOC_CUDA(cudaMemcpyAsync(dB, hB, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    NOALLOC_CUDA_DRAIN(cudaMemcpyAsync(dB, hB, n * sizeof(float), cudaMemcpyHostToDevice, st), st);
     // The library's 256-bit vector kernel at one 2048-element tile per CTA (the three sub-arrays
     // start 4 MiB apart, so all are 32-byte aligned); results are identical on every kernel shape.
     constexpr int kBlock = 256, kVec = 8;
     const unsigned grid = (unsigned)((n + (size_t)kBlock * kVec - 1) / ((size_t)kBlock * kVec));
     b200v::ew_vec_kernel<B200V_OP_VECTORADD, kVec, 1, kBlock, b200v::LD_PLAIN, b200v::ST_PLAIN>
         <<<grid, kBlock, 0, st>>>(dC, dA, dB, 0.0f, n);
-    NOALLOC_CUDA(cudaGetLastError());
-    NOALLOC_CUDA(cudaMemcpyAsync(hC, dC, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    NOALLOC_CUDA_DRAIN(cudaGetLastError(), st);
+    NOALLOC_CUDA_DRAIN(cudaMemcpyAsync(hC, dC, n * sizeof(float), cudaMemcpyDeviceToHost, st), st);
     NOALLOC_CUDA(cudaStreamSynchronize(st));
     return B200V_OK;
 }
