@@ -23,6 +23,7 @@ import "C"
 import (
 	"flag"
 	"fmt"
+	"io"
 	"math"
 	"net/http"
 	"os"
@@ -31,7 +32,6 @@ import (
 	"runtime"
 	"strconv"
 	"strings"
-	"sync"
 	"time"
 	"unsafe"
 )
@@ -150,7 +150,7 @@ func (g *glibcRand) next() int32 {
 
 // runVectorAddSample mirrors run_vectoradd_sample: host init, device add through the C ABI, the
 // sample's verification loop, then a bitwise check.
-func runVectorAddSample(dev int, n uint64, injectFault int64) int {
+func runVectorAddSample(dev int, n uint64, injectFault int64, timingOut *C.b200v_timing, beforeDevice func()) int {
 	runtime.LockOSThread() // CUDA's current device is per OS thread
 	defer runtime.UnlockOSThread()
 	fmt.Printf("[Vector addition of %d elements]\n", n)
@@ -161,6 +161,9 @@ func runVectorAddSample(dev int, n uint64, injectFault int64) int {
 		a[i] = float32(rng.next()) / randMax
 		b[i] = float32(rng.next()) / randMax
 	}
+	if beforeDevice != nil {
+		beforeDevice() // fan-out children meet here: host init done, GPU work next
+	}
 	fmt.Println("Copy input data from the host memory to the CUDA device")
 	var t C.b200v_timing
 	rc := C.b200v_vectoradd(C.int(dev), (*C.float)(unsafe.Pointer(&a[0])), (*C.float)(unsafe.Pointer(&b[0])),
@@ -168,6 +171,9 @@ func runVectorAddSample(dev int, n uint64, injectFault int64) int {
 	if rc != 0 {
 		fmt.Fprintf(os.Stderr, "Failed to launch vectorAdd kernel (error code %s)!\n", strerror(rc))
 		return 1
+	}
+	if timingOut != nil {
+		*timingOut = t
 	}
 	fmt.Printf("CUDA kernel launch with %d blocks of %d threads\n", int(t.grid), int(t.block))
 	fmt.Println("Copy output data from the CUDA device to the host memory")
@@ -190,6 +196,192 @@ func runVectorAddSample(dev int, n uint64, injectFault int64) int {
 	fmt.Println("Test PASSED")
 	fmt.Println("Done")
 	return 0
+}
+
+// fanOut mirrors fan_out: one child process per device (exit-code isolation), held at a start
+// barrier until all are ready, each handing back one JSON row.  The child finds its pipe ends in
+// B200V_FANOUT_FDS="ready_w,go_r,result_w" (ExtraFiles puts them at descriptors 3, 4, 5).
+func fanOut(c *config, use int, args []string) ([]int, []string) {
+	results, rows := make([]int, use), make([]string, use)
+	self, _ := os.Executable()
+	readyR, readyW, _ := os.Pipe()
+	goR, goW, _ := os.Pipe()
+	cmds := make([]*exec.Cmd, use)
+	resR := make([]*os.File, use)
+	for i := 0; i < use; i++ {
+		r, w, _ := os.Pipe()
+		cmd := exec.Command(self, args...)
+		cmd.Env = append(os.Environ(), "B200V_CHILD_DEVICE="+strconv.Itoa(i), "B200V_FANOUT_FDS=3,4,5")
+		cmd.ExtraFiles = []*os.File{readyW, goR, w}
+		cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
+		if err := cmd.Start(); err != nil {
+			results[i] = 1
+		} else {
+			cmds[i] = cmd
+		}
+		w.Close()
+		resR[i] = r
+	}
+	readyW.Close()
+	goR.Close()
+	limit := time.Duration(envInt("B200V_FANOUT_BARRIER_TIMEOUT_S", 300)) * time.Second
+	readyR.SetReadDeadline(time.Now().Add(limit))
+	buf := make([]byte, 64)
+	for arrived := 0; arrived < use; {
+		n, err := readyR.Read(buf)
+		if n <= 0 || err != nil {
+			break // every writer gone, or the timeout: release whoever is waiting
+		}
+		arrived += n
+	}
+	goW.Close()
+	readyR.Close()
+	for i, cmd := range cmds {
+		if cmd != nil {
+			if err := cmd.Wait(); err != nil {
+				results[i] = 1
+			}
+		}
+		b, _ := io.ReadAll(resR[i])
+		resR[i].Close()
+		rows[i] = string(b)
+	}
+	return results, rows
+}
+
+// fanoutChildMain mirrors fanout_child_main: one device, no status files, one result row.
+func fanoutChildMain(c *config) int {
+	var readyW, goR, resW *os.File
+	var a, b, d int
+	if n, _ := fmt.Sscanf(envOr("B200V_FANOUT_FDS", ""), "%d,%d,%d", &a, &b, &d); n == 3 {
+		readyW, goR, resW = os.NewFile(uintptr(a), "ready"), os.NewFile(uintptr(b), "go"), os.NewFile(uintptr(d), "result")
+	}
+	dev := c.childDevice
+	inj := int64(-1)
+	if d := envInt("B200V_INJECT_DEVICE", -1); d < 0 || d == dev {
+		inj = c.injectFault
+	}
+	var warm [48]float32 // context and streams exist before the barrier
+	C.b200v_vectoradd(C.int(dev), (*C.float)(unsafe.Pointer(&warm[0])), (*C.float)(unsafe.Pointer(&warm[16])),
+		(*C.float)(unsafe.Pointer(&warm[32])), 16, nil)
+	meet := func() {
+		if readyW != nil {
+			readyW.Write([]byte{1})
+			readyW.Close()
+		}
+		if goR != nil {
+			io.ReadAll(goR) // returns when the parent closes its end
+			goR.Close()
+		}
+	}
+	var t C.b200v_timing
+	rc := runVectorAddSample(dev, c.elems, inj, &t, meet)
+	bytes := 12.0 * float64(c.elems)
+	gbs := func(ms float64) float64 {
+		if ms <= 0 {
+			return 0
+		}
+		return bytes / (ms * 1e-3) / 1e9
+	}
+	passed := 0
+	if rc == 0 {
+		passed = 1
+	}
+	row := fmt.Sprintf("{\"mode\":\"fanout-child\",\"gpu\":%d,\"elems\":%d,\"passed\":%d,\"h2d_ms\":%.4f,"+
+		"\"kernel_ms\":%.4f,\"d2h_ms\":%.4f,\"total_ms\":%.4f,\"kernel_launches\":%d,\"kernel_gbs\":%.1f,\"e2e_gbs\":%.2f",
+		dev, c.elems, passed, float64(t.h2d_ms), float64(t.kernel_ms), float64(t.d2h_ms), float64(t.total_ms),
+		int(t.kernel_launches), gbs(float64(t.kernel_ms)), gbs(float64(t.total_ms)))
+	hbmLog2 := envInt("B200V_FANOUT_HBM_LOG2", -1)
+	if hbmLog2 < 0 {
+		hbmLog2 = 0
+		if c.elems >= 1<<22 {
+			for uint64(2)<<uint(hbmLog2) <= c.elems {
+				hbmLog2++
+			}
+		}
+	}
+	rc2 := 0
+	if rc == 0 && hbmLog2 > 0 && hbmLog2 <= 32 {
+		var r C.b200v_stream_result
+		src := C.b200v_stream(C.int(dev), C.B200V_OP_VECTORADD, C.size_t(1)<<uint(hbmLog2), 0,
+			C.uint64_t(0xB200+0x1000*uint64(dev)), 5, 20, &r)
+		if src != 0 || r.mismatches != 0 {
+			fmt.Fprintf(os.Stderr, "device-resident vectorAdd on gpu %d failed: %s\n", dev, strerror(src))
+			rc2 = 1
+		}
+		row += fmt.Sprintf(",\"hbm_log2_n\":%d,\"hbm_median_ms\":%.5f,\"hbm_median_gbs\":%.1f,\"hbm_best_gbs\":%.1f,"+
+			"\"hbm_mismatches\":%d,\"hbm_digest\":\"%016x\"", hbmLog2, float64(r.median_ms), float64(r.median_gbs),
+			float64(r.best_gbs), uint64(r.mismatches), uint64(r.digest))
+	}
+	if resW != nil {
+		resW.WriteString(row + "}\n")
+		resW.Close()
+	}
+	if rc == 0 && rc2 == 0 {
+		return 0
+	}
+	return 1
+}
+
+// reportFanout mirrors report_fanout: the children's rows, then the whole-node line and the
+// fanout-bandwidth.prom file (B200V_WRITE_PROM).
+func reportFanout(c *config, use int, rows []string) {
+	num := func(row, key string, dflt float64) float64 {
+		k := "\"" + key + "\":"
+		at := strings.Index(row, k)
+		if at < 0 {
+			return dflt
+		}
+		rest := row[at+len(k):]
+		end := strings.IndexAny(rest, ",}")
+		if end < 0 {
+			end = len(rest)
+		}
+		if v, err := strconv.ParseFloat(strings.Trim(rest[:end], "\""), 64); err == nil {
+			return v
+		}
+		return dflt
+	}
+	var perHbm, perE2e []string
+	var sumHbm, slowHbm, slowTotal, hbmBytes float64
+	prom := "# HELP b200v_fanout_hbm_bandwidth_gbs device-resident vectorAdd GB/s of each GPU, all GPUs running at once\n" +
+		"# TYPE b200v_fanout_hbm_bandwidth_gbs gauge\n"
+	reported := 0
+	for i, row := range rows {
+		if row == "" {
+			continue
+		}
+		reported++
+		fmt.Print(row)
+		if hbm := num(row, "hbm_median_gbs", -1); hbm >= 0 {
+			sumHbm += hbm
+			slowHbm = math.Max(slowHbm, num(row, "hbm_median_ms", 0))
+			hbmBytes = 12.0 * math.Ldexp(1, int(num(row, "hbm_log2_n", 0)))
+			perHbm = append(perHbm, fmt.Sprintf("%.1f", hbm))
+			prom += fmt.Sprintf("b200v_fanout_hbm_bandwidth_gbs{gpu=\"%d\"} %.1f\n", i, hbm)
+		}
+		slowTotal = math.Max(slowTotal, num(row, "total_ms", 0))
+		perE2e = append(perE2e, fmt.Sprintf("%.2f", num(row, "e2e_gbs", 0)))
+	}
+	if reported == 0 {
+		return
+	}
+	jobHbm, jobE2e := 0.0, 0.0
+	if slowHbm > 0 {
+		jobHbm = float64(len(perHbm)) * hbmBytes / (slowHbm * 1e-3) / 1e9
+	}
+	if slowTotal > 0 {
+		jobE2e = float64(reported) * 12.0 * float64(c.elems) / (slowTotal * 1e-3) / 1e9
+	}
+	fmt.Printf("{\"mode\":\"fanout\",\"gpus\":%d,\"reported\":%d,\"elems\":%d,\"per_gpu_hbm_gbs\":[%s],"+
+		"\"sum_hbm_gbs\":%.1f,\"aggregate_hbm_gbs\":%.1f,\"slowest_hbm_ms\":%.5f,\"per_gpu_e2e_gbs\":[%s],"+
+		"\"aggregate_e2e_gbs\":%.2f,\"slowest_total_ms\":%.4f}\n", use, reported, c.elems, strings.Join(perHbm, ","),
+		sumHbm, jobHbm, slowHbm, strings.Join(perE2e, ","), jobE2e, slowTotal)
+	if len(perHbm) > 0 && envBool("B200V_WRITE_PROM", false) {
+		prom += fmt.Sprintf("# HELP b200v_fanout_hbm_aggregate_gbs all GPUs' bytes over the slowest GPU's time\n"+
+			"# TYPE b200v_fanout_hbm_aggregate_gbs gauge\nb200v_fanout_hbm_aggregate_gbs %.1f\n", jobHbm)
+		os.WriteFile(statusPath(c, "fanout-bandwidth.prom"), []byte(prom), 0o644)
+	}
 }
 
 // validateCuda mirrors validate_cuda: one validator instance per device, status files per device,
@@ -225,25 +417,13 @@ func validateCuda(c *config) int {
 		use = c.gpus
 	}
 	results := make([]int, use)
-	if use == 1 {
-		results[0] = runVectorAddSample(0, c.elems, c.injectFault)
+	if use == 1 && !envBool("B200V_FANOUT_FORCE", false) { // one device: in this process, as upstream
+		results[0] = runVectorAddSample(0, c.elems, c.injectFault, nil, nil)
 	} else {
-		self, _ := os.Executable()
-		var wg sync.WaitGroup
-		for i := 0; i < use; i++ {
-			wg.Add(1)
-			go func(i int) { // one child process per device: exit-code isolation
-				defer wg.Done()
-				cmd := exec.Command(self, "--component", "cuda", "--output-dir", c.outputDir, "--elems",
-					strconv.FormatUint(c.elems, 10))
-				cmd.Env = append(os.Environ(), "B200V_CHILD_DEVICE="+strconv.Itoa(i))
-				cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
-				if err := cmd.Run(); err != nil {
-					results[i] = 1
-				}
-			}(i)
-		}
-		wg.Wait()
+		var rows []string
+		results, rows = fanOut(c, use, []string{"--component", "cuda", "--output-dir", c.outputDir, "--elems",
+			strconv.FormatUint(c.elems, 10)})
+		reportFanout(c, use, rows)
 	}
 	all := true
 	for i, rc := range results {
@@ -360,13 +540,15 @@ func validatePlugin(c *config) int {
 		return 1
 	}
 	fmt.Printf("node advertises nvidia.com/gpu: %d\n", gpus)
-	if c.withWorkload && runVectorAddSample(0, c.elems, c.injectFault) != 0 {
+	if c.withWorkload && runVectorAddSample(0, c.elems, c.injectFault, nil, nil) != 0 {
 		return 1
 	}
 	if err := createStatusFile(c, "plugin-ready"); err != nil {
 		fmt.Fprintf(os.Stderr, "unable to create status file plugin-ready: %v\n", err)
 		return 1
 	}
+	// upstream's file is empty; the advertised count is kept in it for the metrics mode
+	os.WriteFile(statusPath(c, "plugin-ready"), []byte(fmt.Sprintf("nvidia.com/gpu: %d\n", gpus)), 0o644)
 	fmt.Println("plugin validation is successful")
 	return 0
 }
@@ -392,8 +574,16 @@ func renderMetrics(c *config) string {
 		idx := strings.TrimSuffix(strings.TrimPrefix(filepath.Base(f), "cuda-gpu"), "-ready")
 		fmt.Fprintf(&b, "b200v_node_cuda_gpu_ready{gpu=\"%s\"} 1\n", idx)
 	}
-	fmt.Fprintf(&b, "# HELP gpu_operator_node_device_plugin_devices_total GPUs that passed cuda validation on this node\n"+
-		"# TYPE gpu_operator_node_device_plugin_devices_total gauge\ngpu_operator_node_device_plugin_devices_total %d\n", len(perGPU))
+	advertised := int64(0) // what plugin validation read from the node's allocatable nvidia.com/gpu
+	if raw, err := os.ReadFile(statusPath(c, "plugin-ready")); err == nil {
+		if at := strings.Index(string(raw), "nvidia.com/gpu:"); at >= 0 {
+			if v, err := strconv.ParseInt(strings.TrimSpace(string(raw)[at+len("nvidia.com/gpu:"):]), 10, 64); err == nil && v > 0 {
+				advertised = v
+			}
+		}
+	}
+	fmt.Fprintf(&b, "# HELP gpu_operator_node_device_plugin_devices_total GPUs the device plugin advertises on this node (allocatable nvidia.com/gpu seen by plugin validation)\n"+
+		"# TYPE gpu_operator_node_device_plugin_devices_total gauge\ngpu_operator_node_device_plugin_devices_total %d\n", advertised)
 	proms, _ := filepath.Glob(statusPath(c, "*.prom"))
 	for _, f := range proms {
 		if raw, err := os.ReadFile(f); err == nil {
@@ -410,22 +600,7 @@ func runStreamSweep(c *config) int {
 	}{{C.B200V_OP_COPY, "copy"}, {C.B200V_OP_SCALE, "scale"}, {C.B200V_OP_ADD, "add"}, {C.B200V_OP_TRIAD, "triad"}}
 	failures := 0
 	if c.childDevice < 0 && c.gpus > 1 { // one sweep per device, each in its own process, all at once
-		self, _ := os.Executable()
-		var wg sync.WaitGroup
-		results := make([]int, c.gpus)
-		for i := 0; i < c.gpus; i++ {
-			wg.Add(1)
-			go func(i int) {
-				defer wg.Done()
-				cmd := exec.Command(self, "--mode", "stream")
-				cmd.Env = append(os.Environ(), "B200V_CHILD_DEVICE="+strconv.Itoa(i))
-				cmd.Stdout, cmd.Stderr = os.Stdout, os.Stderr
-				if err := cmd.Run(); err != nil {
-					results[i] = 1
-				}
-			}(i)
-		}
-		wg.Wait()
+		results, _ := fanOut(c, c.gpus, []string{"--mode", "stream"})
 		for i, rc := range results {
 			if rc != 0 {
 				fmt.Fprintf(os.Stderr, "stream sweep failed on gpu %d (exit code %d)\n", i, rc)
@@ -438,11 +613,21 @@ func runStreamSweep(c *config) int {
 		return 0
 	}
 	dev := 0
-	if c.childDevice >= 0 {
-		dev = c.childDevice
-	}
 	runtime.LockOSThread()
 	defer runtime.UnlockOSThread()
+	if c.childDevice >= 0 { // per-GPU sweeps start together: create the context, then meet the others
+		dev = c.childDevice
+		var warm C.b200v_info
+		C.b200v_device_info(C.int(dev), &warm)
+		var a, b, d int
+		if n, _ := fmt.Sscanf(envOr("B200V_FANOUT_FDS", ""), "%d,%d,%d", &a, &b, &d); n == 3 {
+			readyW, goR := os.NewFile(uintptr(a), "ready"), os.NewFile(uintptr(b), "go")
+			readyW.Write([]byte{1})
+			readyW.Close()
+			io.ReadAll(goR)
+			goR.Close()
+		}
+	}
 	for lg := envInt("B200V_MIN_LOG2", 18); lg <= envInt("B200V_MAX_LOG2", 32); lg++ {
 		for _, op := range ops {
 			var r C.b200v_stream_result
@@ -544,7 +729,7 @@ func main() {
 		os.Exit(1)
 	}
 	if c.childDevice >= 0 {
-		os.Exit(runVectorAddSample(c.childDevice, c.elems, c.injectFault))
+		os.Exit(fanoutChildMain(c))
 	}
 	for tries := 0; ; {
 		rc := -1

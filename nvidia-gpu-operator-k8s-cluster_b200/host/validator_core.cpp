@@ -10,9 +10,11 @@
 #include <csignal>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <dirent.h>
 #include <fcntl.h>
 #include <netinet/in.h>
+#include <poll.h>
 #include <sys/socket.h>
 #include <sys/stat.h>
 #include <sys/types.h>
@@ -192,7 +194,8 @@ long long verify_result(const float *A, const float *B, const float *C, size_t n
     return -1;
 }
 
-int run_vectoradd_sample(const Api &api, int dev, size_t n, long long inject_fault, FILE *out, FILE *err) {
+int run_vectoradd_sample(const Api &api, int dev, size_t n, long long inject_fault, FILE *out, FILE *err,
+                         b200v_timing *timing_out, const std::function<void()> *before_device) {
     std::fprintf(out, "[Vector addition of %zu elements]\n", n);
     float *A = (float *)std::malloc(n ? n * sizeof(float) : 1);
     float *B = (float *)std::malloc(n ? n * sizeof(float) : 1);
@@ -211,10 +214,12 @@ int run_vectoradd_sample(const Api &api, int dev, size_t n, long long inject_fau
         A[i] = std::rand() / (float)RAND_MAX;
         B[i] = std::rand() / (float)RAND_MAX;
     }
+    if (before_device) (*before_device)();   // fan-out children meet here: host init done, GPU work next
     std::fprintf(out, "Copy input data from the host memory to the CUDA device\n");
     b200v_timing t;
     std::memset(&t, 0, sizeof t);
     int rc = api.vectoradd(dev, A, B, C, n, &t);
+    if (timing_out) *timing_out = t;
     if (rc != B200V_OK) {
         std::fprintf(err, "Failed to launch vectorAdd kernel (error code %s)!\n", api.strerror(rc));
         return 1;
@@ -251,14 +256,37 @@ int run_command(const std::string &cmd) {
     return 128 + (WIFSIGNALED(st) ? WTERMSIG(st) : 0);
 }
 
-std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::string> &argv) {
+// Fan-out plumbing.  Three kinds of pipe connect the parent to its per-device children:
+//   ready   every child writes one byte once its GPU context exists and its host inputs are filled
+//   go      the parent closes the write end when all children are ready (or after
+//           B200V_FANOUT_BARRIER_TIMEOUT_S); children block on the read end until then, so the GPU
+//           phases of all devices start together (SURVEY.md §8d cfg3 "started behind a barrier")
+//   result  one per child: its JSON result row, read by the parent after the child exits
+// The child learns its three descriptors from B200V_FANOUT_FDS="ready_w,go_r,result_w".
+std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::string> &argv,
+                         std::vector<std::string> *rows) {
     std::vector<pid_t> pids((size_t)ndev, -1);
     std::vector<int> results((size_t)ndev, 1);
+    if (rows) rows->assign((size_t)ndev, std::string());
+    int ready[2] = {-1, -1}, go[2] = {-1, -1};
+    std::vector<int> res_r((size_t)ndev, -1);
+    const bool piped = ::pipe2(ready, O_CLOEXEC) == 0 && ::pipe2(go, O_CLOEXEC) == 0;
     std::fflush(nullptr);
     for (int i = 0; i < ndev; ++i) {
+        int res[2] = {-1, -1};
+        const bool have_res = piped && ::pipe2(res, O_CLOEXEC) == 0;
         pid_t pid = ::fork();
         if (pid == 0) {
             ::setenv("B200V_CHILD_DEVICE", std::to_string(i).c_str(), 1);
+            if (have_res) {
+                // only these three survive the exec; every other pipe end is close-on-exec
+                for (int fd : {ready[1], go[0], res[1]}) ::fcntl(fd, F_SETFD, 0);
+                const std::string fds = std::to_string(ready[1]) + "," + std::to_string(go[0]) + "," +
+                                        std::to_string(res[1]);
+                ::setenv("B200V_FANOUT_FDS", fds.c_str(), 1);
+            } else {
+                ::unsetenv("B200V_FANOUT_FDS");
+            }
             std::vector<char *> av;
             av.push_back(const_cast<char *>(cfg.self_exe.c_str()));
             for (const std::string &a : argv) av.push_back(const_cast<char *>(a.c_str()));
@@ -267,17 +295,228 @@ std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::str
             ::_exit(127);
         }
         pids[(size_t)i] = pid;
+        if (have_res) {
+            ::close(res[1]);
+            res_r[(size_t)i] = res[0];
+        }
+    }
+    if (piped) {
+        // The barrier: wait for one byte per child.  A child that dies early closes its end, and
+        // when every writer is gone read() returns 0, so a failed child cannot wedge the others
+        // beyond the timeout.
+        ::close(ready[1]);
+        ::close(go[0]);
+        int arrived = 0;
+        const int limit_ms = env_int("B200V_FANOUT_BARRIER_TIMEOUT_S", 300) * 1000;
+        struct timespec t0;
+        ::clock_gettime(CLOCK_MONOTONIC, &t0);
+        while (arrived < ndev) {
+            struct timespec now;
+            ::clock_gettime(CLOCK_MONOTONIC, &now);
+            const long waited = (now.tv_sec - t0.tv_sec) * 1000L + (now.tv_nsec - t0.tv_nsec) / 1000000L;
+            if (waited >= limit_ms) break;
+            struct pollfd pfd = {ready[0], POLLIN, 0};
+            const int pr = ::poll(&pfd, 1, (int)(limit_ms - waited));
+            if (pr < 0 && errno == EINTR) continue;
+            if (pr <= 0) break;
+            char buf[64];
+            const ssize_t got = ::read(ready[0], buf, sizeof buf);
+            if (got <= 0) break;
+            arrived += (int)got;
+        }
+        ::close(go[1]);          // releases every child blocked on the go pipe
+        ::close(ready[0]);
+    } else {
+        for (int fd : {ready[0], ready[1], go[0], go[1]}) if (fd >= 0) ::close(fd);
     }
     for (int i = 0; i < ndev; ++i) {
-        if (pids[(size_t)i] < 0) continue;
-        int st = 0;
-        if (::waitpid(pids[(size_t)i], &st, 0) < 0) continue;
-        results[(size_t)i] = WIFEXITED(st) ? WEXITSTATUS(st) : 128 + (WIFSIGNALED(st) ? WTERMSIG(st) : 0);
+        if (pids[(size_t)i] >= 0) {
+            int st = 0;
+            if (::waitpid(pids[(size_t)i], &st, 0) >= 0)
+                results[(size_t)i] = WIFEXITED(st) ? WEXITSTATUS(st) : 128 + (WIFSIGNALED(st) ? WTERMSIG(st) : 0);
+        }
+        if (res_r[(size_t)i] >= 0) {
+            // a row is far smaller than a pipe buffer, so the child never blocked writing it
+            std::string row;
+            char buf[4096];
+            ssize_t got;
+            while ((got = ::read(res_r[(size_t)i], buf, sizeof buf)) > 0) row.append(buf, (size_t)got);
+            ::close(res_r[(size_t)i]);
+            if (rows) (*rows)[(size_t)i] = row;
+        }
     }
     return results;
 }
 
+FanoutChannel::FanoutChannel() {
+    const std::string v = env_or("B200V_FANOUT_FDS", "");
+    int a = -1, b = -1, c = -1;
+    if (std::sscanf(v.c_str(), "%d,%d,%d", &a, &b, &c) == 3 && a >= 0 && b >= 0 && c >= 0) {
+        ready_fd = a;
+        go_fd = b;
+        result_fd = c;
+    }
+}
+
+void FanoutChannel::arrive_and_wait() {
+    if (ready_fd >= 0) {
+        const char one = 1;
+        ssize_t ignored = ::write(ready_fd, &one, 1);
+        (void)ignored;
+        ::close(ready_fd);
+        ready_fd = -1;
+    }
+    if (go_fd >= 0) {
+        char buf;
+        while (::read(go_fd, &buf, 1) < 0 && errno == EINTR) {}   // returns 0 when the parent closes it
+        ::close(go_fd);
+        go_fd = -1;
+    }
+}
+
+void FanoutChannel::report(const std::string &row) {
+    if (result_fd < 0) return;
+    size_t off = 0;
+    while (off < row.size()) {
+        const ssize_t w = ::write(result_fd, row.data() + off, row.size() - off);
+        if (w <= 0) break;
+        off += (size_t)w;
+    }
+    ::close(result_fd);
+    result_fd = -1;
+}
+
+FanoutChannel::~FanoutChannel() {
+    // a child that leaves without arriving must not hold the others up: closing the write end of
+    // `ready` is what lets the parent see that nobody else is coming
+    for (int *fd : {&ready_fd, &go_fd, &result_fd})
+        if (*fd >= 0) ::close(*fd);
+}
+
+namespace {
+// Value of "key":<number> in a flat JSON row written by this file (no nesting, no escapes).
+double row_number(const std::string &row, const std::string &key, double dflt) {
+    const std::string k = "\"" + key + "\":";
+    const size_t at = row.find(k);
+    if (at == std::string::npos) return dflt;
+    char *end = nullptr;
+    const double v = std::strtod(row.c_str() + at + k.size(), &end);
+    return end && end != row.c_str() + at + k.size() ? v : dflt;
+}
+}  // namespace
+
+// One fan-out child: validates exactly one device, writes no status file (the parent does), and
+// hands the parent one JSON row with what it measured.
+int fanout_child_main(const Api &api, const Config &cfg, FILE *out, FILE *err) {
+    FanoutChannel ch;
+    const int dev = cfg.child_device;
+    const long long inj = (env_int("B200V_INJECT_DEVICE", -1) < 0 || env_int("B200V_INJECT_DEVICE", -1) == dev)
+                              ? cfg.inject_fault : -1;
+    // Create the GPU context (and the library's streams) before the barrier, so that what starts
+    // together after it is GPU work and not context creation.
+    {
+        float a[16] = {0}, b[16] = {0}, c[16];
+        (void)api.vectoradd(dev, a, b, c, 16, nullptr);
+    }
+    const std::function<void()> meet = [&ch] { ch.arrive_and_wait(); };
+    b200v_timing t;
+    std::memset(&t, 0, sizeof t);
+    const int rc = run_vectoradd_sample(api, dev, cfg.elems, inj, out, err, &t, &meet);
+    const double bytes = 12.0 * (double)cfg.elems;
+    char row[1024];
+    int len = std::snprintf(row, sizeof row,
+                            "{\"mode\":\"fanout-child\",\"gpu\":%d,\"elems\":%zu,\"passed\":%d,\"h2d_ms\":%.4f,"
+                            "\"kernel_ms\":%.4f,\"d2h_ms\":%.4f,\"total_ms\":%.4f,\"kernel_launches\":%d,"
+                            "\"kernel_gbs\":%.1f,\"e2e_gbs\":%.2f",
+                            dev, cfg.elems, rc == 0 ? 1 : 0, t.h2d_ms, t.kernel_ms, t.d2h_ms, t.total_ms,
+                            t.kernel_launches, t.kernel_ms > 0 ? bytes / (t.kernel_ms * 1e-3) / 1e9 : 0.0,
+                            t.total_ms > 0 ? bytes / (t.total_ms * 1e-3) / 1e9 : 0.0);
+    // Device-resident HBM figure (cfg3's "aggregate HBM GB/s"): the same vectorAdd kernel on arrays
+    // generated on the GPU, one launch per timed sample.  On for validation sizes that are HBM-bound
+    // anyway (B200V_ELEMS >= 2^22), or at the size B200V_FANOUT_HBM_LOG2 names; 0 turns it off.
+    int hbm_log2 = env_int("B200V_FANOUT_HBM_LOG2", -1);
+    if (hbm_log2 < 0) {
+        hbm_log2 = 0;
+        if (cfg.elems >= ((size_t)1 << 22))
+            while (((size_t)2 << hbm_log2) <= cfg.elems) ++hbm_log2;
+    }
+    int rc2 = 0;
+    if (rc == 0 && hbm_log2 > 0 && hbm_log2 <= 32) {
+        b200v_stream_result r;
+        std::memset(&r, 0, sizeof r);
+        const int src = api.stream(dev, B200V_OP_VECTORADD, (size_t)1 << hbm_log2, 0.0f,
+                                   0xB200ull + 0x1000ull * (uint64_t)dev, 5, 20, &r);
+        if (src != B200V_OK || r.mismatches) {
+            std::fprintf(err, "device-resident vectorAdd on gpu %d failed: %s\n", dev,
+                         api.strerror(src != B200V_OK ? src : B200V_E_MISMATCH));
+            rc2 = 1;
+        }
+        len += std::snprintf(row + len, sizeof row - (size_t)len,
+                             ",\"hbm_log2_n\":%d,\"hbm_median_ms\":%.5f,\"hbm_median_gbs\":%.1f,\"hbm_best_gbs\":%.1f,"
+                             "\"hbm_mismatches\":%" PRIu64 ",\"hbm_digest\":\"%016" PRIx64 "\"",
+                             hbm_log2, r.median_ms, r.median_gbs, r.best_gbs, r.mismatches, r.digest);
+    }
+    std::snprintf(row + len, sizeof row - (size_t)len, "}\n");
+    ch.report(row);
+    return (rc == 0 && rc2 == 0) ? 0 : 1;
+}
+
 // ---- COMPONENT handlers --------------------------------------------------------------------------------
+
+namespace {
+void write_prom(const Config &cfg, const std::string &file, const std::string &text);
+
+// Prints every child's row, then the whole-node figures: per-GPU and summed
+// device-resident HBM GB/s, the job figure "all GPUs' bytes over the slowest GPU's time", and
+// the same for the host-buffer call.  Leaves fanout-bandwidth.prom for the metrics mode.
+void report_fanout(const Config &cfg, int ndev, const std::vector<std::string> &rows, FILE *out) {
+    std::string per_hbm, per_e2e;
+    double sum_hbm = 0, slowest_hbm_ms = 0, slowest_total_ms = 0, hbm_bytes = 0;
+    int with_hbm = 0, reported = 0;
+    std::string prom = "# HELP b200v_fanout_hbm_bandwidth_gbs device-resident vectorAdd GB/s of each GPU, all GPUs running at once\n"
+                       "# TYPE b200v_fanout_hbm_bandwidth_gbs gauge\n";
+    for (int i = 0; i < ndev; ++i) {
+        const std::string &row = rows[(size_t)i];
+        if (row.empty()) continue;
+        ++reported;
+        std::fputs(row.c_str(), out);
+        const double hbm = row_number(row, "hbm_median_gbs", -1.0), hbm_ms = row_number(row, "hbm_median_ms", 0.0);
+        const double e2e = row_number(row, "e2e_gbs", 0.0), total_ms = row_number(row, "total_ms", 0.0);
+        char buf[128];
+        if (hbm >= 0) {
+            ++with_hbm;
+            sum_hbm += hbm;
+            slowest_hbm_ms = std::max(slowest_hbm_ms, hbm_ms);
+            hbm_bytes = 12.0 * std::ldexp(1.0, (int)row_number(row, "hbm_log2_n", 0.0));
+            std::snprintf(buf, sizeof buf, "%s%.1f", per_hbm.empty() ? "" : ",", hbm);
+            per_hbm += buf;
+            std::snprintf(buf, sizeof buf, "b200v_fanout_hbm_bandwidth_gbs{gpu=\"%d\"} %.1f\n", i, hbm);
+            prom += buf;
+        }
+        slowest_total_ms = std::max(slowest_total_ms, total_ms);
+        std::snprintf(buf, sizeof buf, "%s%.2f", per_e2e.empty() ? "" : ",", e2e);
+        per_e2e += buf;
+    }
+    if (!reported) return;
+    const double job_hbm = slowest_hbm_ms > 0 ? with_hbm * hbm_bytes / (slowest_hbm_ms * 1e-3) / 1e9 : 0.0;
+    const double job_e2e = slowest_total_ms > 0 ? reported * 12.0 * (double)cfg.elems / (slowest_total_ms * 1e-3) / 1e9 : 0.0;
+    std::fprintf(out,
+                 "{\"mode\":\"fanout\",\"gpus\":%d,\"reported\":%d,\"elems\":%zu,\"per_gpu_hbm_gbs\":[%s],"
+                 "\"sum_hbm_gbs\":%.1f,\"aggregate_hbm_gbs\":%.1f,\"slowest_hbm_ms\":%.5f,\"per_gpu_e2e_gbs\":[%s],"
+                 "\"aggregate_e2e_gbs\":%.2f,\"slowest_total_ms\":%.4f}\n",
+                 ndev, reported, cfg.elems, per_hbm.c_str(), sum_hbm, job_hbm, slowest_hbm_ms, per_e2e.c_str(), job_e2e,
+                 slowest_total_ms);
+    std::fflush(out);
+    if (with_hbm) {
+        char buf[512];
+        std::snprintf(buf, sizeof buf,
+                      "# HELP b200v_fanout_hbm_aggregate_gbs all GPUs' bytes over the slowest GPU's time\n"
+                      "# TYPE b200v_fanout_hbm_aggregate_gbs gauge\nb200v_fanout_hbm_aggregate_gbs %.1f\n", job_hbm);
+        prom += buf;
+        write_prom(cfg, "fanout-bandwidth.prom", prom);
+    }
+}
+}  // namespace
 
 int validate_cuda(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     if (!delete_status_file(cfg, "cuda-ready") || !delete_per_gpu_files(cfg)) {
@@ -308,13 +547,17 @@ int validate_cuda(const Api &api, const Config &cfg, FILE *out, FILE *err) {
     }
     const int use = cfg.gpus > 0 ? cfg.gpus : ndev;
     std::vector<int> results;
-    if (use == 1) {
+    // One device: the sample runs in this process, as upstream's does.  B200V_FANOUT_FORCE=1 sends
+    // even a single device through the child-process path (start barrier, result row, aggregate).
+    if (use == 1 && !parse_bool(env_or("B200V_FANOUT_FORCE", ""), false)) {
         results.push_back(run_vectoradd_sample(api, 0, cfg.elems, cfg.inject_fault, out, err));
     } else {
         // One validator instance per device: independent shards, no exchange.
         std::vector<std::string> args = {"--component", "cuda", "--output-dir", cfg.output_dir, "--elems",
                                          std::to_string(cfg.elems)};
-        results = fan_out(cfg, use, args);
+        std::vector<std::string> rows;
+        results = fan_out(cfg, use, args, &rows);
+        report_fanout(cfg, use, rows, out);
     }
     bool all = true;
     for (int i = 0; i < use; ++i) {
@@ -449,6 +692,12 @@ int validate_plugin(const Api &api, const Config &cfg, FILE *out, FILE *err) {
         std::fprintf(err, "unable to create status file plugin-ready: %s\n", std::strerror(errno));
         return 1;
     }
+    // Upstream's file is empty and only its presence is read; the count the device plugin
+    // advertised is kept in it so the metrics mode can export it without a Kubernetes client.
+    if (FILE *f = std::fopen(status_path(cfg, "plugin-ready").c_str(), "wb")) {
+        std::fprintf(f, "nvidia.com/gpu: %lld\n", gpus);
+        std::fclose(f);
+    }
     std::fprintf(out, "plugin validation is successful\n");
     return 0;
 }
@@ -490,9 +739,17 @@ std::string render_metrics(const Config &cfg) {
     m += "# HELP b200v_node_cuda_gpu_ready 1 for every GPU whose own vectorAdd validation passed\n";
     m += "# TYPE b200v_node_cuda_gpu_ready gauge\n";
     for (const std::string &l : gpu_lines) m += l;
-    m += "# HELP gpu_operator_node_device_plugin_devices_total GPUs that passed cuda validation on this node\n";
+    // Upstream's meaning: the GPU count the device plugin advertises, i.e. what plugin validation
+    // read from the node's allocatable nvidia.com/gpu and left in plugin-ready (0 until it has run).
+    long long advertised = 0;
+    {
+        bool ok = false;
+        const std::string text = read_file(status_path(cfg, "plugin-ready"), ok);
+        if (ok) advertised = std::max(0LL, number_after(text, "nvidia.com/gpu"));
+    }
+    m += "# HELP gpu_operator_node_device_plugin_devices_total GPUs the device plugin advertises on this node (allocatable nvidia.com/gpu seen by plugin validation)\n";
     m += "# TYPE gpu_operator_node_device_plugin_devices_total gauge\n";
-    m += "gpu_operator_node_device_plugin_devices_total " + std::to_string(gpu_lines.size()) + "\n";
+    m += "gpu_operator_node_device_plugin_devices_total " + std::to_string(advertised) + "\n";
     // Several result files may describe the same metric family (one file per GPU): its HELP and
     // TYPE lines go out once.
     std::vector<std::string> seen_meta;
@@ -612,6 +869,13 @@ int run_stream_sweep(const Api &api, const Config &cfg, FILE *out, FILE *err) {
         return bad ? 1 : 0;
     }
     const int dev = cfg.child_device >= 0 ? cfg.child_device : 0;
+    if (cfg.child_device >= 0) {
+        // per-GPU sweeps start together: create the context, then meet the other children
+        b200v_info warm;
+        api.device_info(dev, &warm);
+        FanoutChannel ch;
+        ch.arrive_and_wait();
+    }
     const int lo = env_int("B200V_MIN_LOG2", 18), hi = env_int("B200V_MAX_LOG2", 32);
     const int ops[] = {B200V_OP_COPY, B200V_OP_SCALE, B200V_OP_ADD, B200V_OP_TRIAD};
     b200v_info info;
@@ -747,11 +1011,7 @@ int validator_main(const Api &api, int argc, char **argv) {
         return 1;
     }
     if (cfg.component == "metrics") return serve_metrics(cfg, stdout, stderr);
-    if (cfg.child_device >= 0) {   // fan-out child: validate exactly one device, no status files
-        const long long inj = (env_int("B200V_INJECT_DEVICE", -1) < 0 ||
-                               env_int("B200V_INJECT_DEVICE", -1) == cfg.child_device) ? cfg.inject_fault : -1;
-        return run_vectoradd_sample(api, cfg.child_device, cfg.elems, inj, stdout, stderr);
-    }
+    if (cfg.child_device >= 0) return fanout_child_main(api, cfg, stdout, stderr);
     auto once = [&]() -> int {
         if (cfg.component == "cuda") return validate_cuda(api, cfg, stdout, stderr);
         if (cfg.component == "driver") return validate_driver(cfg, stdout, stderr);

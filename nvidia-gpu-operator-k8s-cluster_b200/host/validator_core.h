@@ -76,8 +76,11 @@ bool delete_status_file(const Config &cfg, const std::string &name);   // true w
 
 // The sample: host init with rand(), device add through the C ABI, host verification loop.
 // Prints the sample's lines to `out` / `err`.  Returns 0 on "Test PASSED", 1 otherwise.
+// timing_out (optional) receives the library's timing of the device call; before_device (optional)
+// runs after the host init and before the device call (the fan-out barrier).
 int run_vectoradd_sample(const Api &api, int dev, size_t n, long long inject_fault, FILE *out,
-                         FILE *err);
+                         FILE *err, b200v_timing *timing_out = nullptr,
+                         const std::function<void()> *before_device = nullptr);
 
 // The sample's host verification loop: first index with fabs(A[i]+B[i]-C[i]) > 1e-5, or -1.
 long long verify_result(const float *A, const float *B, const float *C, size_t n);
@@ -112,7 +115,25 @@ int vectoradd_main(const Api &api, int argc, char **argv);
 // Runs a shell command, returns its exit status (-1 if it could not be started).
 int run_command(const std::string &cmd);
 
-// Spawns `self_exe` once per device with B200V_CHILD_DEVICE=i and waits; results[i] = exit code.
-std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::string> &argv);
+// Spawns `self_exe` once per device with B200V_CHILD_DEVICE=i, holds the children at a start
+// barrier until all are ready, and waits; results[i] = exit code, (*rows)[i] = the JSON row child i
+// reported ("" if none).
+std::vector<int> fan_out(const Config &cfg, int ndev, const std::vector<std::string> &argv,
+                         std::vector<std::string> *rows = nullptr);
+
+// The child's end of the fan-out pipes (B200V_FANOUT_FDS); every method is a no-op when the
+// process was not started by fan_out.
+struct FanoutChannel {
+    int ready_fd = -1, go_fd = -1, result_fd = -1;
+    FanoutChannel();                        // reads B200V_FANOUT_FDS
+    FanoutChannel(const FanoutChannel &) = delete;
+    FanoutChannel &operator=(const FanoutChannel &) = delete;
+    void arrive_and_wait();                 // "I am ready", then block until every child is
+    void report(const std::string &row);    // hand the parent this child's result row
+    ~FanoutChannel();
+};
+
+// A fan-out child of COMPONENT=cuda: one device, no status files, one result row.
+int fanout_child_main(const Api &api, const Config &cfg, FILE *out, FILE *err);
 
 }  // namespace b200v_host

@@ -261,7 +261,13 @@ def test_metrics_oneshot_reflects_status_files_and_bandwidth(fake, tmp_path):
     assert ts["gpu_operator_node_driver_validation_last_success_ts_seconds"] == 0
     assert abs(ts["gpu_operator_node_cuda_validation_last_success_ts_seconds"] - time.time()) < 300
     assert 'b200v_node_cuda_gpu_ready{gpu="0"} 1' in lines and 'b200v_node_cuda_gpu_ready{gpu="1"} 1' in lines
-    assert "gpu_operator_node_device_plugin_devices_total 2" in lines
+    # upstream's meaning of this gauge: GPUs the device plugin advertises — nothing yet, because
+    # plugin validation has not run; the per-GPU cuda files do not feed it
+    assert "gpu_operator_node_device_plugin_devices_total 0" in lines
+    run(fake, tmp_path, COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=8, WITH_WORKLOAD="false")
+    _rc, out3, _err = run(fake, tmp_path, COMPONENT="metrics", B200V_METRICS_ONESHOT=1)
+    assert "gpu_operator_node_device_plugin_devices_total 8" in out3.splitlines()
+    assert "gpu_operator_node_plugin_ready 1" in out3.splitlines()
     assert any(l.startswith('b200v_hbm_bandwidth_gbs{gpu="0",op="triad",log2_n="28"} ') for l in lines)
     assert 'b200v_nvlink_allreduce_busbw_gbs{impl="nccl",ranks="8",bytes="2048"} 700.00' in lines
     # the hand-written NVLink-multicast probe is the same sweep under B200V_MODE=nvls
@@ -293,3 +299,46 @@ def test_metrics_http_endpoint(fake, tmp_path):
     finally:
         if p.poll() is None:
             p.kill()
+
+
+def test_fanout_children_report_rows_and_the_parent_aggregates(fake, tmp_path):
+    """cfg3 through the product's own fan-out: every child hands the parent one JSON row, the
+    parent prints them, the whole-node line and (with B200V_WRITE_PROM) a .prom file."""
+    rc, out, _err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=4, B200V_ELEMS=1 << 22, B200V_WRITE_PROM=1)
+    assert rc == 0
+    rows = [json.loads(l) for l in out.splitlines() if l.startswith("{")]
+    kids = [r for r in rows if r["mode"] == "fanout-child"]
+    assert sorted(r["gpu"] for r in kids) == [0, 1, 2, 3]
+    for r in kids:
+        assert r["passed"] == 1 and r["elems"] == 1 << 22 and r["hbm_log2_n"] == 22
+        assert r["hbm_mismatches"] == 0 and r["kernel_launches"] == 1
+    (agg,) = [r for r in rows if r["mode"] == "fanout"]
+    assert agg["gpus"] == 4 and agg["reported"] == 4 and len(agg["per_gpu_hbm_gbs"]) == 4
+    # the fake times every launch at 1 ms: 4 GPUs x 12 B x 2^22 elements over 1 ms
+    assert abs(agg["aggregate_hbm_gbs"] - 4 * 12 * (1 << 22) / 1e-3 / 1e9) < 0.2
+    assert abs(agg["sum_hbm_gbs"] - sum(agg["per_gpu_hbm_gbs"])) < 0.5
+    prom = (tmp_path / "fanout-bandwidth.prom").read_text()
+    assert 'b200v_fanout_hbm_bandwidth_gbs{gpu="3"}' in prom and "b200v_fanout_hbm_aggregate_gbs " in prom
+    assert ready(tmp_path) == ["cuda-gpu0-ready", "cuda-gpu1-ready", "cuda-gpu2-ready", "cuda-gpu3-ready",
+                               "cuda-ready"]
+    # the sample's size stays lean: no device-resident measurement unless asked for
+    rc, out, _err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=2)
+    kids = [json.loads(l) for l in out.splitlines() if l.startswith('{"mode":"fanout-child"')]
+    assert rc == 0 and len(kids) == 2 and all("hbm_log2_n" not in r for r in kids)
+    rc, out, _err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=2, B200V_FANOUT_HBM_LOG2=20)
+    kids = [json.loads(l) for l in out.splitlines() if l.startswith('{"mode":"fanout-child"')]
+    assert rc == 0 and all(r["hbm_log2_n"] == 20 for r in kids)
+
+
+def test_fanout_barrier_does_not_wedge_on_a_failing_child(fake, tmp_path):
+    """A child whose GPU fails still arrives at (or abandons) the barrier; the others run, the
+    parent reports the failure and leaves no cuda-ready."""
+    import time
+    t0 = time.time()
+    rc, out, err = run(fake, tmp_path, COMPONENT="cuda", FAKE_NDEV=3, FAKE_MODE="cudaerr", FAKE_FAIL_DEVICE=1,
+                       B200V_FANOUT_BARRIER_TIMEOUT_S=20)
+    assert rc == 1 and time.time() - t0 < 15
+    assert "cuda validation failed on gpu 1" in err
+    assert ready(tmp_path) == ["cuda-gpu0-ready", "cuda-gpu2-ready"]
+    kids = {json.loads(l)["gpu"]: json.loads(l) for l in out.splitlines() if l.startswith('{"mode":"fanout-child"')}
+    assert kids[0]["passed"] == 1 and kids[1]["passed"] == 0 and kids[2]["passed"] == 1

@@ -40,8 +40,20 @@ def test_validator_daemonset_matches_the_product_contract():
         assert env["COMPONENT"] in supported and env["WITH_WAIT"] in ("true", "false")
         mounts = {m["mountPath"] for m in c["volumeMounts"]}
         assert "/run/nvidia/validations" in mounts
-    cuda = inits[2]
-    assert cuda["resources"]["limits"]["nvidia.com/gpu"] == 8
+    # The DaemonSet pod never exits, and Kubernetes reserves max(init requests, sum of app
+    # requests) for a pod's whole life: its effective nvidia.com/gpu request must be 0, or the
+    # validator would keep the node's GPUs away from every tenant (and deadlock a fresh node whose
+    # device plugin waits for this pod's toolkit-ready).
+    def gpus(c):
+        r = c.get("resources", {})
+        return max(int(r.get("limits", {}).get("nvidia.com/gpu", 0)),
+                   int(r.get("requests", {}).get("nvidia.com/gpu", 0)))
+    effective = max(max(gpus(c) for c in inits), sum(gpus(c) for c in spec["containers"]))
+    assert effective == 0
+    assert spec["runtimeClassName"] == "nvidia"
+    for c in inits[2:]:
+        env = {e["name"]: e.get("value") for e in c["env"]}
+        assert env["NVIDIA_VISIBLE_DEVICES"] == "all"
     main = spec["containers"][0]
     assert main["lifecycle"]["preStop"]["exec"]["command"][-1] == "rm -f /run/nvidia/validations/*-ready"
     vols = {v["name"]: v for v in spec["volumes"]}
