@@ -100,9 +100,16 @@ typedef struct b200v_ar_row {
     float    best_ms, median_ms;   /* max over ranks of the per-rank device time */
     double   algbw_gbs;      /* bytes / best time */
     double   busbw_gbs;      /* algbw * 2(n-1)/n */
-    uint64_t mismatches;     /* elements differing from the closed form */
+    uint64_t mismatches;     /* elements differing from the closed form, over the check before the
+                                timed launches and the check after them */
     int      nccl_result;    /* ncclResult_t of the failing call, 0 otherwise */
+    int      algo;           /* hand-written probe: the kernel that ran, B200V_AR_ALGO_*; 0 for NCCL */
 } b200v_ar_row;
+
+#define B200V_AR_ALGO_MULTIMEM 1   /* two-shot, reduction inside the NVSwitch */
+#define B200V_AR_ALGO_P2P      2   /* peer loads + peer stores */
+#define B200V_AR_ALGO_PUSH     3   /* two phases of peer stores */
+#define B200V_AR_ALGO_ONESHOT  4   /* every GPU reduces the whole (small) vector itself */
 
 /* ---- library / device queries ----------------------------------------------------------------- */
 
@@ -207,7 +214,8 @@ int b200v_stream(int dev, int op, size_t n, float s, uint64_t seed, int warmup, 
 /* Single process, one communicator per listed device (ncclCommInitAll).  In-place fp32 sum
  * all-reduce, message sizes min_bytes, 2*min_bytes, ... <= max_bytes; rank r contributes the
  * integer-valued (float)((i*(2r+1) + r) & 15), so the sum is exact in any order and is checked
- * bit for bit against the closed form on the device.
+ * bit for bit against the closed form on the device, once before the timed launches and once
+ * more (re-filled) after them.  Small messages are timed as batches of back-to-back launches.
  * rows must hold max_rows entries; *nrows receives the count written. */
 int b200v_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                           int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
@@ -226,12 +234,15 @@ int b200v_last_nccl_error(void);
 
 /* A second, hand-written NVLink probe (nothing upstream): the same sweep, input
  * pattern, bit-exact check and row format as b200v_allreduce_probe, but the all-reduce is one
- * sm_100a kernel per GPU that reduces inside the NVSwitch (multimem.ld_reduce) and broadcasts
- * through it (multimem.st) over a CUDA multicast object; with 2 GPUs, where the switch has
- * nothing to reduce, the kernel uses plain peer loads/stores over NVLink instead
- * (B200V_NVLS_ALGO=multimem|p2p forces either).  Single process, 2 <= ndev, sizes are
- * multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast
- * support, B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
+ * sm_100a kernel per GPU over a CUDA multicast object and peer mappings.  Which kernel runs
+ * depends on the message size and the GPU count (row.algo says which): one-shot
+ * multimem.ld_reduce for small messages, two phases of peer stores for large messages on 2 and 4
+ * GPUs, multimem.ld_reduce + multimem.st (reduction inside the NVSwitch) otherwise;
+ * B200V_NVLS_ALGO=multimem|p2p|push|oneshot forces one.  Every size is checked twice, before the
+ * timed launches and again after them.  Single process, one host thread per GPU, 1 <= ndev
+ * distinct devices (1 = the identity, which still runs the real kernels), sizes are multiples of
+ * 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast support,
+ * B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
 int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                                int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
 int b200v_last_driver_error(void);
@@ -245,6 +256,36 @@ int b200v_last_driver_error(void);
 int b200v_nvls_allreduce_probe_rank(int dev, int rank, int nranks, const char *rendezvous,
                                     size_t min_bytes, size_t max_bytes, int warmup, int iters,
                                     b200v_ar_row *rows, int max_rows, int *nrows);
+
+/* ---- all-reduce of a CALLER-OWNED device buffer ------------------------
+ * The probes above fill, reduce and check buffers of their own.  These entry points reduce a
+ * buffer the caller filled and will read back, so a checker outside the library (tests/,
+ * bench.py: the CPU oracle's closed form) can compare the reduced bytes.  One process (or host
+ * thread) per GPU; create and destroy are collective; every rank must issue the same sequence of
+ * all-reduce calls with the same counts.  In-place fp32 sum over `count` floats at dBuf (device
+ * memory on the communicator's GPU), enqueued on `stream` (cudaStream_t, NULL = default stream)
+ * and not synchronised.  No upstream counterpart. */
+
+/* NCCL: ncclCommInitRank with the id from b200v_nccl_unique_id, then ncclAllReduce on dBuf. */
+typedef struct b200v_ar_comm b200v_ar_comm;
+int b200v_ar_comm_create(int dev, int rank, int nranks,
+                         const unsigned char id[B200V_NCCL_UNIQUE_ID_BYTES], b200v_ar_comm **comm);
+int b200v_ar_comm_allreduce(b200v_ar_comm *comm, float *dBuf, size_t count, void *stream);
+int b200v_ar_comm_destroy(b200v_ar_comm *comm);
+
+/* The hand-written kernels.  They work on the library's own NVLink-mapped allocation (sized for
+ * max_bytes at create), so each call copies dBuf in, reduces, and copies the result back, all on
+ * `stream`; any count with 4 * count <= max_bytes is accepted (the tail is zero-padded to a whole
+ * 16-byte vector), else B200V_E_TOOLARGE.  The two-phase kernels add in rank order, so the
+ * result equals the sequential sum r = 0..n-1 bit for bit on every rank; the switch-side
+ * reduction's order is the hardware's.  b200v_nvls_comm_check synchronises the device and returns
+ * B200V_E_TIMEOUT if any kernel gave up waiting for a peer. */
+typedef struct b200v_nvls_comm b200v_nvls_comm;
+int b200v_nvls_comm_create(int dev, int rank, int nranks, const char *rendezvous, size_t max_bytes,
+                           b200v_nvls_comm **comm);
+int b200v_nvls_comm_allreduce(b200v_nvls_comm *comm, float *dBuf, size_t count, void *stream);
+int b200v_nvls_comm_check(b200v_nvls_comm *comm);
+int b200v_nvls_comm_destroy(b200v_nvls_comm *comm);
 
 /* Releases cached per-device state (streams, events, staging buffers). */
 int b200v_shutdown(void);

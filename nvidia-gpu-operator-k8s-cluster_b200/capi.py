@@ -48,7 +48,10 @@ class StreamResult(ctypes.Structure):
 class ArRow(ctypes.Structure):
     _fields_ = [("bytes", ctypes.c_uint64), ("best_ms", ctypes.c_float), ("median_ms", ctypes.c_float),
                 ("algbw_gbs", ctypes.c_double), ("busbw_gbs", ctypes.c_double),
-                ("mismatches", ctypes.c_uint64), ("nccl_result", ctypes.c_int)]
+                ("mismatches", ctypes.c_uint64), ("nccl_result", ctypes.c_int), ("algo", ctypes.c_int)]
+
+
+AR_ALGO_NAMES = {0: "nccl", 1: "multimem", 2: "p2p", 3: "push", 4: "oneshot"}
 
 
 class B200VError(RuntimeError):
@@ -86,6 +89,13 @@ SIGNATURES = {
     "b200v_nvls_allreduce_probe": (_i, [_i, _P(_i), _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_last_driver_error": (_i, []),
     "b200v_nvls_allreduce_probe_rank": (_i, [_i, _i, _i, ctypes.c_char_p, _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
+    "b200v_ar_comm_create": (_i, [_i, _i, _i, ctypes.c_char_p, _P(_vp)]),
+    "b200v_ar_comm_allreduce": (_i, [_vp, _vp, _sz, _vp]),
+    "b200v_ar_comm_destroy": (_i, [_vp]),
+    "b200v_nvls_comm_create": (_i, [_i, _i, _i, ctypes.c_char_p, _sz, _P(_vp)]),
+    "b200v_nvls_comm_allreduce": (_i, [_vp, _vp, _sz, _vp]),
+    "b200v_nvls_comm_check": (_i, [_vp]),
+    "b200v_nvls_comm_destroy": (_i, [_vp]),
     "b200v_shutdown": (_i, []),
 }
 
@@ -306,6 +316,49 @@ def allreduce_probe_rank(dev, rank, nranks, uid, min_bytes=1024, max_bytes=1 << 
     _check(lib().b200v_allreduce_probe_rank(dev, rank, nranks, uid, min_bytes, max_bytes, warmup, iters,
                                             rows, 64, ctypes.byref(n)), "b200v_allreduce_probe_rank")
     return _rows(rows, n.value)
+
+
+class ArComm:
+    """One rank of an NCCL communicator that all-reduces caller-owned device buffers
+    (b200v_ar_comm_*).  Collective: every rank constructs it, with the id rank 0 made."""
+
+    def __init__(self, dev, rank, nranks, uid):
+        assert len(uid) == NCCL_UNIQUE_ID_BYTES
+        h = _vp()
+        _check(lib().b200v_ar_comm_create(dev, rank, nranks, uid, ctypes.byref(h)), "b200v_ar_comm_create")
+        self.h = h
+
+    def allreduce(self, dBuf, count, stream=None):
+        _check(lib().b200v_ar_comm_allreduce(self.h, _ptr(dBuf), count, stream), "b200v_ar_comm_allreduce")
+
+    def close(self):
+        if self.h:
+            _check(lib().b200v_ar_comm_destroy(self.h), "b200v_ar_comm_destroy")
+            self.h = None
+
+
+class NvlsComm:
+    """One rank of the hand-written NVLink all-reduce on caller-owned device buffers
+    (b200v_nvls_comm_*).  Collective; `rendezvous` names the abstract Unix socket the ranks of this
+    host meet on."""
+
+    def __init__(self, dev, rank, nranks, rendezvous, max_bytes):
+        h = _vp()
+        _check(lib().b200v_nvls_comm_create(dev, rank, nranks, rendezvous.encode(), max_bytes, ctypes.byref(h)),
+               "b200v_nvls_comm_create")
+        self.h = h
+
+    def allreduce(self, dBuf, count, stream=None):
+        _check(lib().b200v_nvls_comm_allreduce(self.h, _ptr(dBuf), count, stream), "b200v_nvls_comm_allreduce")
+
+    def check(self):
+        """Synchronises the device; raises if a kernel gave up waiting for a peer."""
+        _check(lib().b200v_nvls_comm_check(self.h), "b200v_nvls_comm_check")
+
+    def close(self):
+        if self.h:
+            _check(lib().b200v_nvls_comm_destroy(self.h), "b200v_nvls_comm_destroy")
+            self.h = None
 
 
 def nccl_version():

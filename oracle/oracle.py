@@ -129,6 +129,12 @@ def digest_from(a, first_index):
     return int(lib().oracle_digest_from(_words(a), a.size, first_index))
 
 
+def allreduce_input(n, rank):
+    """What rank `rank` contributes to the probe's all-reduce: float((i*(2r+1) + r) & 15)."""
+    i = np.arange(n, dtype=np.int64)
+    return ((i * (2 * rank + 1) + rank) & 15).astype(np.float32)
+
+
 def allreduce_expected(n, nranks):
     """Closed form of the probe's reduced buffer: sum over r of float((i*(2r+1) + r) & 15)."""
     i = np.arange(n, dtype=np.int64)

@@ -1,0 +1,145 @@
+"""GPU parity tests of the all-reduce on CALLER-OWNED device buffers (b200v_ar_comm_* over NCCL,
+b200v_nvls_comm_* over the hand-written NVLink kernels): the test fills each rank's buffer, the
+library reduces it in place, the test reads it back and compares it byte for byte with the CPU
+oracle's closed form — nothing inside the library judges the result.
+
+On a one-GPU lease the collective has one rank (the sum is the input), which still runs the real
+communicator set-up, the real kernels (multimem instructions included) and the staging copies.
+With two or more GPUs the ranks run as host threads of this process, one per GPU.
+"""
+import os
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SIZES = (1003, 4096, (1 << 18) + 5, 1 << 22)          # floats: ragged, tiny, ragged mid, 16 MiB
+
+
+def _nranks(gpu):
+    return 1 if gpu < 2 else (2 if gpu < 4 else (4 if gpu < 8 else 8))
+
+
+def _run_ranks(nranks, fn):
+    """fn(rank) on one host thread per rank; re-raises the first failure."""
+    errs = [None] * nranks
+
+    def wrap(r):
+        try:
+            fn(r)
+        except BaseException as e:      # noqa: BLE001 - reported below
+            errs[r] = e
+    th = [threading.Thread(target=wrap, args=(r,)) for r in range(nranks)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for e in errs:
+        if e is not None:
+            raise e
+
+
+def _reduce_and_compare(make_comm, nranks, oracle, sizes, repeats=1):
+    import torch
+    got = {}
+
+    def rank_fn(r):
+        torch.cuda.set_device(r)
+        comm = make_comm(r)
+        try:
+            for n in sizes:
+                buf = torch.from_numpy(oracle.allreduce_input(n, r)).cuda(r)
+                guard = torch.full((n + 64,), -77.0, device="cuda:%d" % r)
+                guard[:n] = buf
+                st = torch.cuda.current_stream(r).cuda_stream
+                for _ in range(repeats):                     # back to back, nothing in between
+                    comm.allreduce(guard.data_ptr(), n, stream=st)
+                torch.cuda.synchronize(r)
+                if hasattr(comm, "check"):
+                    comm.check()
+                host = guard.cpu().numpy()
+                assert (host[n:] == -77.0).all(), "wrote past the end at n=%d" % n
+                got[(r, n)] = host[:n].copy()
+        finally:
+            comm.close()
+    _run_ranks(nranks, rank_fn)
+    for n in sizes:
+        want = oracle.allreduce_expected(n, nranks) * np.float32(nranks ** (repeats - 1))
+        for r in range(nranks):
+            assert got[(r, n)].tobytes() == want.tobytes(), "rank %d n=%d repeats=%d" % (r, n, repeats)
+
+
+def test_nccl_comm_allreduce_matches_the_oracle(capi, gpu, oracle):
+    nranks = _nranks(gpu)
+    uid = capi.nccl_unique_id()
+    _reduce_and_compare(lambda r: capi.ArComm(r, r, nranks, uid), nranks, oracle, SIZES)
+    uid = capi.nccl_unique_id()
+    _reduce_and_compare(lambda r: capi.ArComm(r, r, nranks, uid), nranks, oracle, SIZES[:3], repeats=3)
+
+
+@pytest.mark.parametrize("algo", ["auto", "multimem", "oneshot", "p2p", "push"])
+def test_nvls_comm_allreduce_matches_the_oracle(capi, gpu, oracle, algo, monkeypatch):
+    nranks = _nranks(gpu)
+    if algo == "push" and nranks == 1:
+        pytest.skip("the two-phase push kernel needs a peer: covered from 2 GPUs up")
+    if algo == "auto":
+        monkeypatch.delenv("B200V_NVLS_ALGO", raising=False)
+    else:
+        monkeypatch.setenv("B200V_NVLS_ALGO", algo)
+    name = "b200v-comm-test-%d-%s" % (os.getpid(), algo)
+    max_bytes = 4 * max(SIZES) + 64
+
+    def make(r):
+        try:
+            return capi.NvlsComm(r, r, nranks, name, max_bytes)
+        except capi.B200VError as e:
+            if e.code == capi.E_UNSUPPORTED:
+                pytest.skip("no multicast support on this box (%d rank(s))" % nranks)
+            raise
+    _reduce_and_compare(make, nranks, oracle, SIZES)
+    name += "-b2b"
+    _reduce_and_compare(make, nranks, oracle, SIZES[:3], repeats=3)
+
+
+def test_nvls_comm_rejects_what_it_cannot_hold(capi, gpu):
+    import torch
+    try:
+        comm = capi.NvlsComm(0, 0, 1, "b200v-comm-small-%d" % os.getpid(), 1 << 20)
+    except capi.B200VError as e:
+        if e.code == capi.E_UNSUPPORTED:
+            pytest.skip("no multicast support on this box")
+        raise
+    try:
+        buf = torch.zeros(4 << 20, device="cuda:0")
+        with pytest.raises(capi.B200VError) as ei:
+            comm.allreduce(buf.data_ptr(), buf.numel())
+        assert ei.value.code == capi.E_TOOLARGE
+        comm.allreduce(buf.data_ptr(), 0)                    # empty: a no-op
+        with pytest.raises(capi.B200VError) as ei:
+            comm.allreduce(None, 16)
+        assert ei.value.code == capi.E_BADARG
+    finally:
+        comm.close()
+
+
+def test_nvls_probe_single_device_runs_the_real_kernels(capi, gpu, monkeypatch):
+    """One rank: the all-reduce is the identity, but the multimem / one-shot / peer kernels, the
+    barrier flags and the per-CTA epoch bookkeeping all run for real on a one-GPU lease."""
+    seen = set()
+    for algo in ("auto", "multimem", "p2p", "oneshot"):
+        if algo == "auto":
+            monkeypatch.delenv("B200V_NVLS_ALGO", raising=False)
+        else:
+            monkeypatch.setenv("B200V_NVLS_ALGO", algo)
+        try:
+            rows = capi.nvls_allreduce_probe([0], min_bytes=1 << 10, max_bytes=1 << 24, warmup=1, iters=3)
+        except capi.B200VError as e:
+            if e.code == capi.E_UNSUPPORTED:
+                pytest.skip("no multicast support with a single device on this box")
+            raise
+        assert [r.bytes for r in rows] == [1 << k for k in range(10, 25)]
+        assert all(r.mismatches == 0 and r.best_ms > 0 for r in rows), algo
+        seen |= {capi.AR_ALGO_NAMES[r.algo] for r in rows}
+    assert {"multimem", "p2p", "oneshot"} <= seen

@@ -29,7 +29,7 @@ def test_nvls_allreduce_ragged_slices_and_both_algorithms(capi, gpu, monkeypatch
     if gpu < 2:
         pytest.skip("needs at least two GPUs")
     ranks = 2 if gpu < 4 else (4 if gpu < 8 else 8)
-    for algo in ("multimem", "p2p"):
+    for algo in ("multimem", "p2p", "push", "oneshot"):
         monkeypatch.setenv("B200V_NVLS_ALGO", algo)
         try:
             rows = capi.nvls_allreduce_probe(list(range(ranks)), min_bytes=63 * 16, max_bytes=63 * 16 << 12,
@@ -85,8 +85,11 @@ def test_nvls_probe_one_process_per_gpu(capi, gpu, tmp_path):
 
 def test_nvls_probe_argument_checks(capi, gpu):
     with pytest.raises(capi.B200VError) as ei:
-        capi.nvls_allreduce_probe([0], min_bytes=1024, max_bytes=2048)
-    assert ei.value.code == capi.E_BADARG                    # one GPU is not a collective
+        capi.nvls_allreduce_probe([], min_bytes=1024, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG                    # no GPU at all
+    with pytest.raises(capi.B200VError) as ei:
+        capi.nvls_allreduce_probe([0, 0], min_bytes=1024, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG                    # two ranks on one GPU would wait on each other
     with pytest.raises(capi.B200VError) as ei:
         capi.nvls_allreduce_probe([0, gpu + 3], min_bytes=1024, max_bytes=2048)
     assert ei.value.code == capi.E_BADARG
