@@ -178,6 +178,13 @@ int b200v_vectoradd_device(int dev, const float *dA, const float *dB, float *dC,
 int b200v_stream_device(int dev, int op, float *dDst, const float *dX, const float *dY, float s,
                         size_t n, void *stream);
 
+/* Which of the compiled kernels b200v_stream_device would launch for this op, these device
+ * pointers (their alignment and overlap decide) and this n: its name is written to buf, e.g.
+ * "b200v::ew_tile_kernel<VECTORADD,VEC=8,UNROLL=1,BLOCK=1024> (t8u1b1024)".  Launches nothing.
+ * For reports that must name the kernel that actually ran.  No upstream counterpart. */
+int b200v_kernel_name(int op, const float *dDst, const float *dX, const float *dY, size_t n,
+                      char *buf, size_t buflen);
+
 /* The sample's own launch shape — one element per thread, ceil(n/256) blocks of 256 threads,
  * bounds-checked — kept as the in-library cross-check for the tuned kernels.
  * n must fit the 2^31-1 block limit times 256. */
@@ -239,9 +246,8 @@ int b200v_last_nccl_error(void);
  * multimem.ld_reduce for small messages, two phases of peer stores for large messages on 2 and 4
  * GPUs, multimem.ld_reduce + multimem.st (reduction inside the NVSwitch) otherwise;
  * B200V_NVLS_ALGO=multimem|p2p|push|oneshot forces one.  Every size is checked twice, before the
- * timed launches and again after them.  Single process, one host thread per GPU, 1 <= ndev
- * distinct devices (1 = the identity, which still runs the real kernels), sizes are multiples of
- * 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast support,
+ * timed launches and again after them.  Single process, one host thread per GPU, 2 <= ndev
+ * distinct devices (a multicast object cannot be made for one), sizes are multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast support,
  * B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
 int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                                int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
@@ -274,7 +280,7 @@ int b200v_ar_comm_allreduce(b200v_ar_comm *comm, float *dBuf, size_t count, void
 int b200v_ar_comm_destroy(b200v_ar_comm *comm);
 
 /* The hand-written kernels.  They work on the library's own NVLink-mapped allocation (sized for
- * max_bytes at create), so each call copies dBuf in, reduces, and copies the result back, all on
+ * max_bytes at create; 2 <= nranks), so each call copies dBuf in, reduces, and copies the result back, all on
  * `stream`; any count with 4 * count <= max_bytes is accepted (the tail is zero-padded to a whole
  * 16-byte vector), else B200V_E_TOOLARGE.  The two-phase kernels add in rank order, so the
  * result equals the sequential sum r = 0..n-1 bit for bit on every rank; the switch-side

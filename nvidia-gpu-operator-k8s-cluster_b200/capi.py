@@ -76,6 +76,7 @@ SIGNATURES = {
     "b200v_stream_host": (_i, [_i, _i, _vp, _vp, _vp, _f, _sz, _P(Timing)]),
     "b200v_vectoradd_device": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "b200v_stream_device": (_i, [_i, _i, _vp, _vp, _vp, _f, _sz, _vp]),
+    "b200v_kernel_name": (_i, [_i, _vp, _vp, _vp, _sz, ctypes.c_char_p, _sz]),
     "b200v_vectoradd_device_sampleshape": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "b200v_fill_device": (_i, [_i, _vp, _sz, _u64, _vp]),
     "b200v_digest_device": (_i, [_i, _vp, _sz, _P(_u64), _vp]),
@@ -232,6 +233,13 @@ def vectoradd_device(dA, dB, dC, n, dev=0, stream=None):
 def vectoradd_device_sampleshape(dA, dB, dC, n, dev=0, stream=None):
     _check(lib().b200v_vectoradd_device_sampleshape(dev, _ptr(dA), _ptr(dB), _ptr(dC), n, stream),
            "b200v_vectoradd_device_sampleshape")
+
+
+def kernel_name(op, dDst, dX, dY, n):
+    """Name of the kernel the library dispatches for this op and these device pointers."""
+    buf = ctypes.create_string_buffer(256)
+    _check(lib().b200v_kernel_name(op, _ptr(dDst), _ptr(dX), _ptr(dY), n, buf, len(buf)), "b200v_kernel_name")
+    return buf.value.decode()
 
 
 def stream_device(op, dDst, dX, dY, s, n, dev=0, stream=None):

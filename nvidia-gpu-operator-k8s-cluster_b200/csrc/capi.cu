@@ -475,6 +475,11 @@ int b200v_stream_device(int dev, int op, float *dDst, const float *dX, const flo
     return launch_ew(*g.c, op, dDst, dX, dY, s, n, (cudaStream_t)stream, nullptr, nullptr);
 }
 
+int b200v_kernel_name(int op, const float *dDst, const float *dX, const float *dY, size_t n, char *buf,
+                      size_t buflen) {
+    return describe_ew(op, dDst, dX, dY, n, buf, buflen);
+}
+
 int b200v_vectoradd_device(int dev, const float *dA, const float *dB, float *dC, size_t n,
                            void *stream) {
     return b200v_stream_device(dev, B200V_OP_VECTORADD, dC, dA, dB, 0.0f, n, stream);

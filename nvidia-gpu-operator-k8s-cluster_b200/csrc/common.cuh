@@ -60,6 +60,8 @@ int destroy_all_ctx();
 // grid/block (optional) receive the launch shape.
 int launch_ew(const DeviceCtx &ctx, int op, float *dst, const float *x, const float *y, float s,
               size_t n, cudaStream_t stream, int *grid, int *block);
+// Name of the kernel launch_ew would run for these pointers and this n (same decision code).
+int describe_ew(int op, const float *dst, const float *x, const float *y, size_t n, char *buf, size_t len);
 int launch_sampleshape(int op, float *dst, const float *x, const float *y, float s, size_t n,
                        cudaStream_t stream);
 

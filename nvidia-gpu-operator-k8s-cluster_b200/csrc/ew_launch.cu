@@ -4,8 +4,10 @@
 //   * all three pointers 32-byte aligned, dst not overlapping an input  -> tuned vector kernel
 //   * 16-byte aligned only                                               -> 128-bit vector kernel
 //   * anything else (misaligned base, in-place)                          -> grid-stride scalar
-// The default shape is the winner of tools/tune.cu on a B200 (profiles/r01_tune.md); the
+// The default shape is the winner of tools/tune.cu on a B200 (profiles/r01_tune.csv, summarised in
+// profiles/r01_tune_top.txt); the
 // environment variable B200V_EW_VARIANT selects another compiled variant for A/B runs.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -113,6 +115,35 @@ int grid_for(size_t tiles, int sm_count, int ctas_per_sm) {
 
 }  // namespace
 
+// Which compiled shape launch_ew runs for these pointers: -1 = the scalar grid-stride kernel,
+// otherwise an index into g_variants.  One place, so the launch and its description cannot drift.
+static int pick_variant(const float *dst, const float *x, const float *y, size_t n) {
+    const uintptr_t bits = (uintptr_t)dst | (uintptr_t)x | (uintptr_t)y;
+    const bool alias = overlaps(dst, x, n) || overlaps(dst, y, n);
+    if (alias || (bits & 15)) return -1;
+    int vi = env_variant();
+    if (vi < 0) vi = (bits & 31) ? 1 : 0;
+    if ((bits & 31) && g_variants[vi].vec == 8) vi = 1;
+    return vi;
+}
+
+int describe_ew(int op, const float *dst, const float *x, const float *y, size_t n, char *buf, size_t len) {
+    if (op < 0 || op >= B200V_OP_COUNT || !buf || len == 0) return B200V_E_BADARG;
+    static const char *ops[B200V_OP_COUNT] = {"COPY", "SCALE", "ADD", "TRIAD", "VECTORADD", "TRIAD_UNFUSED"};
+    if (!ew_needs_y(op)) y = nullptr;
+    const int vi = pick_variant(dst, x, y, n);
+    if (vi < 0) {
+        std::snprintf(buf, len, "b200v::ew_scalar_kernel<%s>", ops[op]);
+        return B200V_OK;
+    }
+    const Variant &v = g_variants[vi];
+    const char *fam = v.bulk ? "ew_bulk_kernel" : std::strncmp(v.name, "clc", 3) == 0 ? "ew_clc_kernel"
+                    : (v.name[0] == 't' ? "ew_tile_kernel" : "ew_vec_kernel");
+    if (v.bulk) std::snprintf(buf, len, "b200v::%s<%s,tile=%d,block=%d> (%s)", fam, ops[op], v.tile_f, v.block, v.name);
+    else std::snprintf(buf, len, "b200v::%s<%s,VEC=%d,UNROLL=%d,BLOCK=%d> (%s)", fam, ops[op], v.vec, v.unroll, v.block, v.name);
+    return B200V_OK;
+}
+
 int launch_ew(const DeviceCtx &ctx, int op, float *dst, const float *x, const float *y, float s,
               size_t n, cudaStream_t stream, int *grid_out, int *block_out) {
     if (op < 0 || op >= B200V_OP_COUNT) return B200V_E_BADARG;
@@ -124,11 +155,10 @@ int launch_ew(const DeviceCtx &ctx, int op, float *dst, const float *x, const fl
     if (!dst || !x || (ew_needs_y(op) && !y)) return B200V_E_BADARG;
     if (!ew_needs_y(op)) y = nullptr;
 
-    const uintptr_t bits = (uintptr_t)dst | (uintptr_t)x | (uintptr_t)y;
-    const bool alias = overlaps(dst, x, n) || overlaps(dst, y, n);
+    int vi = pick_variant(dst, x, y, n);
 
     int grid, block;
-    if (alias || (bits & 15)) {
+    if (vi < 0) {
         // scalar grid-stride path: 8 elements per thread per pass keeps the grid persistent-sized
         block = 256;
         grid = grid_for((n + 255) / 256, ctx.sm_count, 8);
@@ -138,9 +168,6 @@ int launch_ew(const DeviceCtx &ctx, int op, float *dst, const float *x, const fl
             ew_scalar_kernel<B200V_OP_VECTORADD>, ew_scalar_kernel<B200V_OP_TRIAD_UNFUSED>};
         scalar[op]<<<grid, block, 0, stream>>>(dst, x, y, s, n);
     } else {
-        int vi = env_variant();
-        if (vi < 0) vi = (bits & 31) ? 1 : 0;
-        if ((bits & 31) && g_variants[vi].vec == 8) vi = 1;
         Variant &v = g_variants[vi];
         block = v.block;
         if (v.bulk) {

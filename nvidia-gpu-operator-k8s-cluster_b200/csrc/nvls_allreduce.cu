@@ -743,7 +743,7 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     const bool peers = t.peers_mapped && peer_algo_compiled(n);
     if (tn.forced == ALGO_ONESHOT) return bytes <= kOneShotCap ? ALGO_ONESHOT : ALGO_MULTIMEM;
     if (tn.forced == ALGO_MULTIMEM) return ALGO_MULTIMEM;
-    if (tn.forced == ALGO_P2P) return (peers || (n == 1 && t.peers_mapped)) ? ALGO_P2P : ALGO_MULTIMEM;
+    if (tn.forced == ALGO_P2P) return peers ? ALGO_P2P : ALGO_MULTIMEM;
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
     if (bytes <= tn.oneshot_max) return ALGO_ONESHOT;
     // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
@@ -791,7 +791,7 @@ int launch_allreduce(const Tuning &tn, NvlsTeam &t, NvlsRank &r, int algo, size_
     }
     case ALGO_P2P: {
         ctas = tn.ctas ? tn.ctas : std::min(r.sm_count, 64);
-        auto kern = n == 1 ? p2p_allreduce_kernel<1, 4, true> : n == 2 ? p2p_allreduce_kernel<2, 4, true>
+        auto kern = n == 2 ? p2p_allreduce_kernel<2, 4, true>
                   : n == 4 ? p2p_allreduce_kernel<4, 2, true> : p2p_allreduce_kernel<8, 1, true>;
         kern<<<ctas, kThreads, 0, st>>>(a, data, n4);
         break;
@@ -978,7 +978,8 @@ extern "C" int b200v_last_driver_error(void) { return g_last_cu; }
 extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                                           int warmup, int iters, b200v_ar_row *rows, int max_rows,
                                           int *nrows) {
-    if (ndev < 1 || !devs || bad_probe_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
+    // a multicast object needs at least two devices (cuMulticastCreate refuses one)
+    if (ndev < 2 || !devs || bad_probe_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
         return B200V_E_BADARG;
     *nrows = 0;
     int count = 0;
@@ -1003,7 +1004,7 @@ extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_
 extern "C" int b200v_nvls_allreduce_probe_rank(int dev, int rank, int nranks, const char *rendezvous,
                                                size_t min_bytes, size_t max_bytes, int warmup, int iters,
                                                b200v_ar_row *rows, int max_rows, int *nrows) {
-    if (nranks < 1 || rank < 0 || rank >= nranks || !rendezvous || !*rendezvous ||
+    if (nranks < 2 || rank < 0 || rank >= nranks || !rendezvous || !*rendezvous ||
         bad_probe_args(min_bytes, max_bytes, warmup, iters, rows, max_rows, nrows))
         return B200V_E_BADARG;
     *nrows = 0;
@@ -1043,7 +1044,7 @@ extern "C" int b200v_nvls_comm_create(int dev, int rank, int nranks, const char 
                                       b200v_nvls_comm **out) {
     if (!out) return B200V_E_BADARG;
     *out = nullptr;
-    if (nranks < 1 || rank < 0 || rank >= nranks || !rendezvous || !*rendezvous || max_bytes < 16)
+    if (nranks < 2 || rank < 0 || rank >= nranks || !rendezvous || !*rendezvous || max_bytes < 16)
         return B200V_E_BADARG;
     int count = 0;
     int rc = b200v_device_count(&count);

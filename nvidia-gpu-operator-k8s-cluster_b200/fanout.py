@@ -1,20 +1,10 @@
 """Per-GPU fan-out arithmetic: the validation workload shards with no exchange.
 
 Every rank (one process per GPU) validates its own device on its own arrays; nothing crosses
-ranks on the data path.  These helpers only decide who owns what and how per-rank results are
-folded into the whole-job figure; the same rules are implemented in host/validator_core.cpp for
-the `nvidia-validator` fan-out.
+ranks on the data path.  These helpers only give every rank its own input seed and fold per-rank
+results into the whole-job figure — bench.py uses every one of them; host/validator_core.cpp
+implements the same folding for the `nvidia-validator` fan-out.
 """
-
-
-def shard_range(n, rank, world):
-    """Contiguous element range [lo, hi) of a logical n-element array owned by `rank` of `world`:
-    the first n % world ranks get one extra element."""
-    if world < 1 or not (0 <= rank < world):
-        raise ValueError("bad rank/world %r/%r" % (rank, world))
-    per, rem = divmod(n, world)
-    lo = rank * per + min(rank, rem)
-    return lo, lo + per + (1 if rank < rem else 0)
 
 
 def rank_seed(base_seed, rank):
@@ -27,12 +17,6 @@ def aggregate_gbs(bytes_per_rank, max_seconds):
     if max_seconds <= 0:
         raise ValueError("non-positive time")
     return sum(bytes_per_rank) / max_seconds / 1e9
-
-
-def status_file_names(ndev):
-    """Status files the fan-out leaves under OUTPUT_DIR on success: one per GPU
-    and cuda-ready only when every GPU passed.  All match upstream's preStop `rm -f *-ready`."""
-    return ["cuda-gpu%d-ready" % i for i in range(ndev)] + ["cuda-ready"]
 
 
 # ---- cross-rank folding (torch.distributed is plumbing only: a barrier and two reductions) -------

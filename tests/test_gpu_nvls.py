@@ -85,8 +85,8 @@ def test_nvls_probe_one_process_per_gpu(capi, gpu, tmp_path):
 
 def test_nvls_probe_argument_checks(capi, gpu):
     with pytest.raises(capi.B200VError) as ei:
-        capi.nvls_allreduce_probe([], min_bytes=1024, max_bytes=2048)
-    assert ei.value.code == capi.E_BADARG                    # no GPU at all
+        capi.nvls_allreduce_probe([0], min_bytes=1024, max_bytes=2048)
+    assert ei.value.code == capi.E_BADARG                    # one GPU is not a collective
     with pytest.raises(capi.B200VError) as ei:
         capi.nvls_allreduce_probe([0, 0], min_bytes=1024, max_bytes=2048)
     assert ei.value.code == capi.E_BADARG                    # two ranks on one GPU would wait on each other

@@ -64,9 +64,15 @@ def test_validator_daemonset_matches_the_product_contract():
     assert ex["ports"][0]["containerPort"] == 8000
 
 
-def test_status_files_written_by_the_product_match_the_prestop_glob(pkg):
+def test_status_files_written_by_the_product_match_the_prestop_glob():
     import fnmatch
-    for name in pkg.fanout.status_file_names(8) + ["driver-ready", "toolkit-ready", "plugin-ready"]:
+    import re
+    # every status-file name the product can create, read off its source
+    src = open(os.path.join(ROOT, "nvidia-gpu-operator-k8s-cluster_b200", "host", "validator_core.cpp")).read()
+    names = set(re.findall(r'"([a-z]+-ready)"', src)) | {"cuda-gpu%d-ready" % i for i in range(8)}
+    assert {"cuda-ready", "driver-ready", "toolkit-ready", "plugin-ready"} <= names
+    assert '"cuda-gpu" + std::to_string(i) + "-ready"' in src
+    for name in names:
         assert fnmatch.fnmatch(name, "*-ready")
 
 
