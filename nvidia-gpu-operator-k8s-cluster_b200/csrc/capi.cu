@@ -152,12 +152,15 @@ int acquire_ctx(int dev, DeviceCtx **out) {
 void release_ctx(DeviceCtx *ctx) { static_cast<Slot *>(ctx->owner)->mu.unlock(); }
 
 int destroy_all_ctx() {
+    // The Slot objects themselves are never freed: a thread that has just taken its Slot* in
+    // acquire_ctx (map lock already dropped) must still find a live mutex to lock.  Shutdown
+    // releases what the slots hold — streams, events, device and pinned buffers — under each
+    // slot's own lock; a later call on that device simply builds the context again.
     std::lock_guard<std::mutex> g(g_map_mu);
     for (auto &kv : g_ctx) {
         std::lock_guard<std::mutex> g2(kv.second->mu);
         destroy_ctx(kv.second->ctx);
     }
-    g_ctx.clear();
     return B200V_OK;
 }
 

@@ -3,6 +3,9 @@
 //   b200v-linkbw p2p  [ngpu]   cudaMemcpyPeerAsync between GPU pairs over NVLink, one direction and
 //                              both directions at once — the "link rate" the all-reduce kernels are
 //                              judged against;
+//   b200v-linkbw p2pk          the same pair driven by SM kernels instead of the copy engines: 128- and
+//                              256-bit stores/loads on the peer mapping, and bulk (TMA) copies of
+//                              shared-memory tiles — which mechanism gets how close to the link rate;
 //   b200v-linkbw pcie [ngpu]   host<->device copies: every GPU alone, every pair, groups of 4, all
 //                              at once; H2D only, D2H only, both; with plain pinned, write-combined
 //                              and transparent-huge-page-backed registered host buffers; and what the
@@ -79,6 +82,138 @@ static void p2p_pair(int a, int b, size_t bytes, int iters) {
     std::fflush(stdout);
     CK(cudaSetDevice(a)); cudaFree(pa); cudaFree(qa); cudaStreamDestroy(sa);
     CK(cudaSetDevice(b)); cudaFree(pb); cudaFree(qb); cudaStreamDestroy(sb);
+}
+
+// ---- p2pk: SM-driven peer copies (what an all-reduce kernel's stores and loads look like on the link) ----
+// push: load local, store to the peer.  pull: load from the peer, store local.  128-bit and 256-bit
+// accesses, and the bulk-copy (TMA) engine moving shared-memory tiles to the peer.
+template <int VEC, bool PULL>
+__global__ void __launch_bounds__(512) pk_copy_kernel(float *__restrict__ dst, const float *__restrict__ src, size_t n) {
+    constexpr int U = 4;
+    const size_t nv = n / VEC, stride = (size_t)gridDim.x * 512;
+    for (size_t v0 = (size_t)blockIdx.x * 512 + threadIdx.x; v0 < nv; v0 += stride * U) {
+        float r[U][VEC];
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+            const size_t v = v0 + (size_t)j * stride;
+            if (v < nv) {
+                if constexpr (VEC == 4)
+                    asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r[j][0]), "=f"(r[j][1]), "=f"(r[j][2]), "=f"(r[j][3]) : "l"(src + v * 4));
+                else
+                    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=f"(r[j][0]), "=f"(r[j][1]), "=f"(r[j][2]), "=f"(r[j][3]), "=f"(r[j][4]), "=f"(r[j][5]), "=f"(r[j][6]), "=f"(r[j][7])
+                                 : "l"(src + v * 8));
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+            const size_t v = v0 + (size_t)j * stride;
+            if (v < nv) {
+                if constexpr (VEC == 4)
+                    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(dst + v * 4), "f"(r[j][0]), "f"(r[j][1]), "f"(r[j][2]), "f"(r[j][3]) : "memory");
+                else
+                    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                                 :: "l"(dst + v * 8), "f"(r[j][0]), "f"(r[j][1]), "f"(r[j][2]), "f"(r[j][3]), "f"(r[j][4]), "f"(r[j][5]), "f"(r[j][6]), "f"(r[j][7]) : "memory");
+            }
+        }
+    }
+}
+
+// One thread per CTA drives a ring of STAGES shared-memory tiles: bulk load (local global -> shared),
+// wait, bulk store (shared -> peer global).  TILE bytes per transfer.
+template <int TILE, int STAGES>
+__global__ void __launch_bounds__(32) pk_bulk_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t bytes) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) unsigned long long bar[STAGES];
+    if (threadIdx.x != 0) return;
+    auto sa = [](const void *p) { return (unsigned)__cvta_generic_to_shared(p); };
+    for (int i = 0; i < STAGES; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(sa(&bar[i])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const size_t tiles = bytes / TILE;
+    const size_t mine = tiles > blockIdx.x ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto load = [&](size_t k) {
+        const int s = (int)(k % STAGES);
+        const size_t off = (blockIdx.x + k * gridDim.x) * (size_t)TILE;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(sa(&bar[s])), "r"((unsigned)TILE) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(sa(smem + (size_t)s * TILE)), "l"(src + off), "r"((unsigned)TILE), "r"(sa(&bar[s])) : "memory");
+    };
+    for (size_t k = 0; k < mine && k < (size_t)(STAGES - 1); ++k) load(k);
+    for (size_t k = 0; k < mine; ++k) {
+        const int s = (int)(k % STAGES);
+        const unsigned parity = (unsigned)((k / STAGES) & 1);
+        asm volatile("{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n"
+                     :: "r"(sa(&bar[s])), "r"(parity) : "memory");
+        const size_t off = (blockIdx.x + k * gridDim.x) * (size_t)TILE;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(dst + off), "r"(sa(smem + (size_t)s * TILE)), "r"((unsigned)TILE) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (k + STAGES - 1 < mine) {
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // the slot stored last round is free
+            load(k + STAGES - 1);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+static void p2pk(int a, int b, size_t bytes, int iters) {
+    float *la, *ra_on_b, *lb, *rb_on_a;      // a's source, a's target on b; b's source, b's target on a
+    cudaStream_t sa, sb;
+    cudaEvent_t a0, a1, b0, b1;
+    CK(cudaSetDevice(a)); cudaDeviceEnablePeerAccess(b, 0); (void)cudaGetLastError();
+    CK(cudaMalloc(&la, bytes)); CK(cudaMalloc(&rb_on_a, bytes)); CK(cudaMemset(la, 1, bytes));
+    CK(cudaStreamCreateWithFlags(&sa, cudaStreamNonBlocking)); CK(cudaEventCreate(&a0)); CK(cudaEventCreate(&a1));
+    CK(cudaSetDevice(b)); cudaDeviceEnablePeerAccess(a, 0); (void)cudaGetLastError();
+    CK(cudaMalloc(&lb, bytes)); CK(cudaMalloc(&ra_on_b, bytes)); CK(cudaMemset(lb, 2, bytes));
+    CK(cudaStreamCreateWithFlags(&sb, cudaStreamNonBlocking)); CK(cudaEventCreate(&b0)); CK(cudaEventCreate(&b1));
+    CK(cudaDeviceSynchronize());
+    const size_t n = bytes / 4;
+    struct Var { const char *name; int kind; int ctas; };
+    const Var vars[] = {{"push_v4", 0, 64}, {"push_v4", 0, 148}, {"push_v8", 1, 64}, {"push_v8", 1, 148}, {"pull_v4", 2, 148},
+                        {"pull_v8", 3, 148}, {"bulk_push_16k_s4", 4, 64}, {"bulk_push_16k_s4", 4, 148}, {"bulk_push_32k_s4", 5, 148},
+                        {"bulk_push_8k_s8", 6, 148}, {"bulk_pull_16k_s4", 7, 148}};
+    for (int dev : {a, b}) {
+        CK(cudaSetDevice(dev));
+        CK(cudaFuncSetAttribute(pk_bulk_kernel<32768, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 32768));
+        CK(cudaFuncSetAttribute(pk_bulk_kernel<16384, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 16384));
+        CK(cudaFuncSetAttribute(pk_bulk_kernel<8192, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 8192));
+    }
+    for (const Var &v : vars) {
+        auto launch = [&](int dev, cudaStream_t st, float *src_local, float *dst_remote) {
+            CK(cudaSetDevice(dev));
+            switch (v.kind) {
+            case 0: pk_copy_kernel<4, false><<<v.ctas, 512, 0, st>>>(dst_remote, src_local, n); break;
+            case 1: pk_copy_kernel<8, false><<<v.ctas, 512, 0, st>>>(dst_remote, src_local, n); break;
+            case 2: pk_copy_kernel<4, true><<<v.ctas, 512, 0, st>>>(src_local, dst_remote, n); break;      // read the peer, write local
+            case 3: pk_copy_kernel<8, true><<<v.ctas, 512, 0, st>>>(src_local, dst_remote, n); break;
+            case 4: pk_bulk_kernel<16384, 4><<<v.ctas, 32, 4 * 16384, st>>>((char *)dst_remote, (const char *)src_local, bytes); break;
+            case 5: pk_bulk_kernel<32768, 4><<<v.ctas, 32, 4 * 32768, st>>>((char *)dst_remote, (const char *)src_local, bytes); break;
+            case 6: pk_bulk_kernel<8192, 8><<<v.ctas, 32, 8 * 8192, st>>>((char *)dst_remote, (const char *)src_local, bytes); break;
+            default: pk_bulk_kernel<16384, 4><<<v.ctas, 32, 4 * 16384, st>>>((char *)src_local, (const char *)dst_remote, bytes); break;
+            }
+            CK(cudaGetLastError());
+        };
+        float res[2][2] = {{0, 0}, {0, 0}};
+        for (int bi = 0; bi < 2; ++bi) {
+            for (int rep = 0; rep < 2; ++rep) {
+                CK(cudaSetDevice(a)); CK(cudaEventRecord(a0, sa));
+                if (bi) { CK(cudaSetDevice(b)); CK(cudaEventRecord(b0, sb)); }
+                for (int i = 0; i < iters; ++i) {
+                    launch(a, sa, la, ra_on_b);
+                    if (bi) launch(b, sb, lb, rb_on_a);
+                }
+                CK(cudaSetDevice(a)); CK(cudaEventRecord(a1, sa));
+                if (bi) { CK(cudaSetDevice(b)); CK(cudaEventRecord(b1, sb)); }
+                CK(cudaStreamSynchronize(sa));
+                if (bi) CK(cudaStreamSynchronize(sb));
+            }
+            CK(cudaEventElapsedTime(&res[bi][0], a0, a1));
+            if (bi) CK(cudaEventElapsedTime(&res[bi][1], b0, b1));
+        }
+        const double gb = (double)bytes * iters / 1e9;
+        std::printf("{\"mode\":\"p2pk\",\"kernel\":\"%s\",\"ctas\":%d,\"bytes\":%zu,\"uni_gbs\":%.1f,\"bi_ab_gbs\":%.1f,\"bi_ba_gbs\":%.1f}\n",
+                    v.name, v.ctas, bytes, gb / (res[0][0] * 1e-3), gb / (res[1][0] * 1e-3), gb / (res[1][1] * 1e-3));
+        std::fflush(stdout);
+    }
 }
 
 // ---- pcie ----------------------------------------------------------------------------------------------
@@ -244,7 +379,12 @@ int main(int argc, char **argv) {
         if (ndev > 4) p2p_pair(2, 5, (size_t)1 << 30, 10);
         return 0;
     }
-    if (mode != "pcie") { std::fprintf(stderr, "usage: %s p2p|pcie [ngpu]\n", argv[0]); return 1; }
+    if (mode == "p2pk") {
+        if (ndev < 2) { std::fprintf(stderr, "p2pk needs two GPUs\n"); return 1; }
+        p2pk(0, 1, (size_t)512 << 20, 10);
+        return 0;
+    }
+    if (mode != "pcie") { std::fprintf(stderr, "usage: %s p2p|p2pk|pcie [ngpu]\n", argv[0]); return 1; }
 
     const size_t bytes = (size_t)256 << 20;
     const int iters = 8;                                   // 2 GiB per direction per GPU per measurement

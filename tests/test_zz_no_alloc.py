@@ -79,7 +79,7 @@ def test_noalloc_on_a_second_gpu(capi, gpu, oracle):
 
 def test_noalloc_on_a_caller_stream_and_tiny_sizes(capi, gpu):
     import torch
-    st = torch.cuda.Stream()
+    st = torch.cuda.Stream(device=0)    # explicit: the library leaves whichever GPU it used last current
     for n in (0, 1, 7, 2048, 2049):
         a, b = _inputs(n, 7 + n)
         want = np.zeros(n, np.float32)

@@ -43,7 +43,7 @@ for algo in auto multimem push; do
   B200V_MODE=nvls B200V_GPUS=$N B200V_MIN_LOG2=10 B200V_MAX_LOG2=24 timeout 120 $V > $OUT.small_$algo.jsonl 2>> $OUT.sweep.err
 done
 unset B200V_NVLS_ALGO
-for mx in 65536 262144 1048576; do
+for mx in 131072 1048576; do
   B200V_NVLS_ONESHOT_MAX=$mx B200V_MODE=nvls B200V_GPUS=$N B200V_MIN_LOG2=14 B200V_MAX_LOG2=21 timeout 120 $V > $OUT.oneshot_max_$mx.jsonl 2>> $OUT.sweep.err
 done
 B200V_MODE=nccl B200V_GPUS=$N B200V_MIN_LOG2=10 B200V_MAX_LOG2=30 timeout 300 $V > $OUT.nccl.jsonl 2>> $OUT.sweep.err
