@@ -126,6 +126,12 @@ int b200v_device_info(int dev, b200v_info *out);
  * SURVEY.md §8 a5).  No upstream counterpart. */
 int b200v_host_alloc(void **ptr, size_t bytes);
 int b200v_host_free(void *ptr);
+/* The same with a hint.  B200V_HOST_WRITE_ONLY: the CPU only ever writes this buffer (the input
+ * vectors), so it may be write-combined memory when the library's host-memory policy
+ * (B200V_HOST_POLICY=pinned|wc|thp) says that transfers faster; reading such a buffer from the
+ * CPU is very slow.  Free with b200v_host_free.  No upstream counterpart. */
+#define B200V_HOST_WRITE_ONLY 1
+int b200v_host_alloc_ex(void **ptr, size_t bytes, int flags);
 
 /* ---- the validation workload -------------------------------------------------------------------- */
 

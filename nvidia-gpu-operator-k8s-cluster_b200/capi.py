@@ -71,6 +71,7 @@ SIGNATURES = {
     "b200v_device_info": (_i, [_i, _P(Info)]),
     "b200v_host_alloc": (_i, [_P(_vp), _sz]),
     "b200v_host_free": (_i, [_vp]),
+    "b200v_host_alloc_ex": (_i, [_P(_vp), _sz, _i]),
     "b200v_vectoradd": (_i, [_i, _vp, _vp, _vp, _sz, _P(Timing)]),
     "b200v_vectoradd_noalloc": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "b200v_stream_host": (_i, [_i, _i, _vp, _vp, _vp, _f, _sz, _P(Timing)]),
@@ -163,9 +164,12 @@ def device_info(dev=0):
     return info
 
 
-def host_alloc(nbytes):
+HOST_WRITE_ONLY = 1
+
+
+def host_alloc(nbytes, flags=0):
     p = _vp()
-    _check(lib().b200v_host_alloc(ctypes.byref(p), nbytes), "b200v_host_alloc")
+    _check(lib().b200v_host_alloc_ex(ctypes.byref(p), nbytes, flags), "b200v_host_alloc_ex")
     return p.value
 
 
@@ -177,11 +181,11 @@ class PinnedArray:
     """n elements of pinned host memory from b200v_host_alloc, viewed as a numpy array (.array).
     Freed by close() or when the object is collected; the array must not outlive it."""
 
-    def __init__(self, n, dtype="float32"):
+    def __init__(self, n, dtype="float32", write_only=False):
         import numpy as np
         dt = np.dtype(dtype)
         self.nbytes = max(1, n * dt.itemsize)
-        self.ptr = host_alloc(self.nbytes)
+        self.ptr = host_alloc(self.nbytes, HOST_WRITE_ONLY if write_only else 0)
         buf = (ctypes.c_char * self.nbytes).from_address(self.ptr)
         self.array = np.frombuffer(buf, dtype=dt, count=n)
 

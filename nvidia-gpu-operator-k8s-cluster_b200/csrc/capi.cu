@@ -8,6 +8,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <sys/mman.h>
 #include <vector>
 
 #include "common.cuh"
@@ -446,16 +447,79 @@ int b200v_device_info(int dev, b200v_info *out) {
     return B200V_OK;
 }
 
-int b200v_host_alloc(void **ptr, size_t bytes) {
+// Host buffers the DMA engines can use directly.  Three ways to get one, chosen per call by
+// B200V_HOST_POLICY (default below; profiles/README.md has the measurements behind it):
+//   pinned  cudaHostAlloc, portable
+//   wc      the same, write-combined, for buffers the CPU only writes (B200V_HOST_WRITE_ONLY):
+//           device reads of them need no CPU-cache snoop; the CPU must never read them
+//   thp     anonymous memory advised into transparent huge pages, touched, then cudaHostRegister'ed:
+//           512 x fewer pages for the IOMMU and the DMA page tables to walk
+// The registry remembers how each pointer was made so b200v_host_free can undo it.
+namespace {
+struct HostBlock { int kind; void *raw; size_t raw_bytes; };
+std::mutex g_host_mu;
+std::map<void *, HostBlock> g_host_blocks;
+enum { HOST_PINNED = 0, HOST_WC = 1, HOST_THP = 2 };
+
+int host_policy() {
+    const char *e = std::getenv("B200V_HOST_POLICY");
+    if (e && !std::strcmp(e, "wc")) return HOST_WC;
+    if (e && !std::strcmp(e, "thp")) return HOST_THP;
+    return HOST_PINNED;
+}
+}  // namespace
+
+int b200v_host_alloc_ex(void **ptr, size_t bytes, int flags) {
     if (!ptr) return B200V_E_BADARG;
     *ptr = nullptr;
     if (bytes == 0) return B200V_OK;
-    B200V_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+    int kind = host_policy();
+    if (kind == HOST_WC && !(flags & B200V_HOST_WRITE_ONLY)) kind = HOST_PINNED;   // the CPU reads results
+    HostBlock blk{kind, nullptr, 0};
+    void *p = nullptr;
+    if (kind == HOST_THP) {
+        const size_t huge = (size_t)2 << 20;
+        blk.raw_bytes = (bytes + huge - 1) / huge * huge + huge;
+        blk.raw = ::mmap(nullptr, blk.raw_bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (blk.raw == MAP_FAILED) return B200V_E_NOMEM;
+        p = (void *)(((uintptr_t)blk.raw + huge - 1) / huge * huge);
+        ::madvise(p, blk.raw_bytes - huge, MADV_HUGEPAGE);
+        for (size_t off = 0; off < bytes; off += 4096) ((volatile char *)p)[off] = 0;   // fault in before pinning
+        cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            ::munmap(blk.raw, blk.raw_bytes);
+            return (int)e;
+        }
+    } else {
+        B200V_CUDA(cudaHostAlloc(&p, bytes, cudaHostAllocPortable | (kind == HOST_WC ? cudaHostAllocWriteCombined : 0)));
+    }
+    {
+        std::lock_guard<std::mutex> g(g_host_mu);
+        g_host_blocks[p] = blk;
+    }
+    *ptr = p;
     return B200V_OK;
 }
 
+int b200v_host_alloc(void **ptr, size_t bytes) { return b200v_host_alloc_ex(ptr, bytes, 0); }
+
 int b200v_host_free(void *ptr) {
     if (!ptr) return B200V_OK;
+    HostBlock blk{HOST_PINNED, nullptr, 0};
+    {
+        std::lock_guard<std::mutex> g(g_host_mu);
+        auto it = g_host_blocks.find(ptr);
+        if (it != g_host_blocks.end()) {
+            blk = it->second;
+            g_host_blocks.erase(it);
+        }
+    }
+    if (blk.kind == HOST_THP) {
+        B200V_CUDA(cudaHostUnregister(ptr));
+        ::munmap(blk.raw, blk.raw_bytes);
+        return B200V_OK;
+    }
     B200V_CUDA(cudaFreeHost(ptr));
     return B200V_OK;
 }

@@ -724,7 +724,7 @@ Tuning read_tuning() {
         if (v >= 1 && v <= kMaxCtas) t.ctas = v;
     }
     if (const char *e = std::getenv("B200V_NVLS_UNROLL")) t.unroll = std::atoi(e);
-    t.oneshot_max = 256 * 1024;
+    t.oneshot_max = 0;               // 0 = by rank count, see choose_algo
     if (const char *e = std::getenv("B200V_NVLS_ONESHOT_MAX")) t.oneshot_max = (size_t)std::atoll(e);
     if (t.oneshot_max > kOneShotCap) t.oneshot_max = kOneShotCap;
     if (const char *e = std::getenv("B200V_NVLS_TIMEOUT_MS")) {
@@ -745,7 +745,11 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_MULTIMEM) return ALGO_MULTIMEM;
     if (tn.forced == ALGO_P2P) return peers ? ALGO_P2P : ALGO_MULTIMEM;
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
-    if (bytes <= tn.oneshot_max) return ALGO_ONESHOT;
+    // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
+    // latency-bound.  Measured crossover (profiles/README.md): ~1 MiB at 2 and 4 GPUs
+    // (512 KiB: 15.0 vs 21.2 us at 2, 16.0 vs 17.3 us at 4), earlier at 8 where the traffic is 8x.
+    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n <= 4 ? kOneShotCap : (size_t)256 << 10);
+    if (bytes <= oneshot_max) return ALGO_ONESHOT;
     // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
     // 4 GPUs the switch-side reduction moves fewer bytes per GPU.  (Measured: profiles/README.md.)
     if (n == 2 && peers) return ALGO_PUSH;
