@@ -36,6 +36,9 @@ for ctas in 8 24 32; do
   B200V_NVLS_CTAS=$ctas B200V_MODE=nvls B200V_GPUS=$N B200V_MIN_LOG2=30 B200V_MAX_LOG2=30 timeout 60 $B/nvidia-validator >> $OUT.multimem_ctas.jsonl 2>> $OUT.ar.err
 done
 
+B200V_MODE=nvls B200V_GPUS=$N B200V_MIN_LOG2=10 B200V_MAX_LOG2=30 timeout 200 $B/nvidia-validator > $OUT.nvls.jsonl 2>> $OUT.ar.err
+timeout 100 $B/b200v-linkbw p2p $N > $OUT.p2p.jsonl 2>> $OUT.ar.err
+
 rm -f $OUTPUT_DIR/*-ready
 B200V_ELEMS=268435456 B200V_GPUS=$N B200V_WRITE_PROM=1 COMPONENT=cuda timeout 300 $B/nvidia-validator > $OUT.fanout.log 2>&1
 echo "fanout rc=$? files: $(ls $OUTPUT_DIR | tr '\n' ' ')" >> $OUT.fanout.log
