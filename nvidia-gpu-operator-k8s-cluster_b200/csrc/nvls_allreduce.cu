@@ -747,8 +747,9 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
     // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
     // latency-bound.  Measured crossover (profiles/README.md): ~1 MiB at 2 and 4 GPUs
-    // (512 KiB: 15.0 vs 21.2 us at 2, 16.0 vs 17.3 us at 4), earlier at 8 where the traffic is 8x.
-    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n <= 4 ? kOneShotCap : (size_t)256 << 10);
+    // (512 KiB: 15.0 vs 21.2 us at 2, 16.0 vs 17.3 us at 4), 512 KiB at 8 where the traffic is 8x
+    // (512 KiB: 19.1 vs 22.0 us; 1 MiB: 24.9 vs 23.1 us).
+    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n <= 4 ? kOneShotCap : (size_t)512 << 10);
     if (bytes <= oneshot_max) return ALGO_ONESHOT;
     // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
     // 4 GPUs the switch-side reduction moves fewer bytes per GPU.  (Measured: profiles/README.md.)
