@@ -60,7 +60,7 @@ constexpr size_t kFlagBytes = 64 * 1024;      // barrier words live in front of 
 constexpr int kMaxCtas = 4096;
 constexpr int kThreads = 512;
 // One-shot messages are at most this long; the data region always holds two such input slots.
-constexpr size_t kOneShotCap = (size_t)1 << 20;
+constexpr size_t kOneShotCap = (size_t)4 << 20;
 constexpr int kMaxPeers = 8;
 
 struct Drv {
@@ -262,15 +262,32 @@ oneshot_allreduce_kernel(ArArgs a, size_t in_off, float *__restrict__ out, size_
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
     const float *mc = reinterpret_cast<const float *>(a.mc_base + in_off);
-    const unsigned epoch = load_epoch(a);
-    const unsigned nr = (unsigned)a.nranks;
-    if (!gpu_barrier(mc_flag, uc_flag, epoch + nr, a.timeout_ns)) {
-        if (threadIdx.x == 0) atomicExch(a.err, 1);
-        return;
+    // The lean form of gpu_barrier, for the latency-bound case.  This kernel has written nothing
+    // before its only barrier — the input slot was filled by earlier work on the stream, which is
+    // complete and in this GPU's L2 at the kernel boundary — so the arrival needs no system-wide
+    // fence of its own: the release on the reduction is enough.  The arrival is sent first and the
+    // CTA's epoch word is fetched while it is in flight.
+    __shared__ int ok_s;
+    if (threadIdx.x == 0) {
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc_flag), "r"(1u) : "memory");
+        const unsigned target = a.epochs[blockIdx.x] + (unsigned)a.nranks;
+        const unsigned long long t0 = now_ns();
+        int ok = 1;
+        unsigned polls = 0;
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(uc_flag) : "memory");
+            if ((int)(v - target) >= 0) break;
+            if ((++polls & 1023u) == 0 && now_ns() - t0 > a.timeout_ns) { ok = 0; break; }
+        }
+        a.epochs[blockIdx.x] = target;
+        if (!ok) atomicExch(a.err, 1);
+        ok_s = ok;
     }
+    __syncthreads();
+    if (!ok_s) return;
     for (size_t v = (size_t)blockIdx.x * kThreads + threadIdx.x; v < n4; v += (size_t)gridDim.x * kThreads)
         st_f4<false>(out + 4 * v, mm_ld_reduce(mc + 4 * v));
-    store_epoch(a, epoch + nr);
 }
 
 // ---- p2p: plain peer loads and stores, pull the slice from everyone, push the sum to everyone ---------
@@ -746,10 +763,10 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_P2P) return peers ? ALGO_P2P : ALGO_MULTIMEM;
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
     // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
-    // latency-bound.  Measured crossover (profiles/README.md): ~1 MiB at 2 and 4 GPUs
-    // (512 KiB: 15.0 vs 21.2 us at 2, 16.0 vs 17.3 us at 4), 512 KiB at 8 where the traffic is 8x
-    // (512 KiB: 19.1 vs 22.0 us; 1 MiB: 24.9 vs 23.1 us).
-    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n <= 4 ? kOneShotCap : (size_t)512 << 10);
+    // latency-bound.  Measured crossovers (profiles/README.md): 2 MiB at 2 GPUs (18.5 vs 23.3 us;
+    // at 4 MiB 28.3 vs 25.7 us), 1 MiB at 4, 512 KiB at 8 where the traffic is 8x.
+    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max
+                             : (n == 2 ? (size_t)2 << 20 : n <= 4 ? (size_t)1 << 20 : (size_t)512 << 10);
     if (bytes <= oneshot_max) return ALGO_ONESHOT;
     // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
     // 4 GPUs the switch-side reduction moves fewer bytes per GPU.  (Measured: profiles/README.md.)
