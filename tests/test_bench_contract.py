@@ -60,3 +60,43 @@ def test_recorded_b200_lines_keep_the_contract(name):
         assert d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["kind"] == "port"
     else:
         assert d["allreduce"]["bit_exact"] is True
+
+
+@pytest.mark.parametrize("name", ["r02_bench_n1.json", "r02_bench_n8.json"])
+def test_round2_lines_carry_what_the_verdict_asked_for(name):
+    with open(os.path.join(ROOT, "profiles", name)) as f:
+        d = json.loads(f.read().strip())
+    assert BASE_KEYS <= set(d)
+    n = d["config"]["elements_per_array"]
+    expect = d["n_gpus"] * 12 * n / (d["ms_per_step"] * 1e-3) / 1e9
+    assert abs(d["value"] - expect) / expect < 1e-3
+    r = d["roofline"]
+    # the kernel is named by the library's dispatch, the traffic figure says where it comes from,
+    # and the same launch was held for at least two seconds
+    assert r["kernel"].startswith("b200v::ew_tile_kernel<VECTORADD,VEC=8,UNROLL=1,BLOCK=1024>")
+    assert "profiles/traffic.json" in r["traffic_source"]
+    assert r["sustained"]["seconds"] >= 1.99 and r["sustained"]["launches"] > 1000
+    assert abs(r["sustained"]["gbs_per_gpu"] - r["achieved"]) / r["achieved"] < 0.02
+    assert not {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(d["clocks"]["reasons"])
+    assert d["gpu_launches"] == d["steps"] * d["n_gpus"]
+    if d["n_gpus"] == 1:
+        sweep = d["stream_sweep"]
+        assert sweep["digest_failures"] == 0 and sweep["mem_bus_bits"] == 7680
+        rows = [x for x in sweep["rows"] if "op" in x]
+        assert {x["log2_n"] for x in rows} == {18, 22, 24, 26, 28, 30, 32}
+        assert {x["op"] for x in rows} == {"copy", "scale", "add", "triad"}
+        assert all(x["digest_ok"] and x["checked_vs"].startswith("oracle") for x in rows)
+        assert all(("frac_of_8000" in x) == (not x["l2_resident"]) for x in rows)
+        c = d["cpu_baseline"]
+        assert c["kind"] == "port" and c["cores"] > 1 and c["single_thread"]["cores"] == 1
+        assert c["value"] > c["single_thread"]["value"]
+    else:
+        for key in ("allreduce", "nvls_allreduce"):
+            a = d[key]
+            assert a["bit_exact"] is True
+            p = a["allreduce_parity"]
+            assert p["checked_vs"] == "oracle" and p["mismatches"] == 0 and len(p["sizes_bytes"]) >= 3
+            assert any(b % 16 for b in p["sizes_bytes"])                  # a ragged size is among them
+            assert a["rows"][0]["bytes"] == 1024 and a["rows"][-1]["bytes"] == 1 << 30
+        kernels = {x["kernel"] for x in d["nvls_allreduce"]["rows"]}
+        assert "oneshot" in kernels and len(kernels) >= 2
