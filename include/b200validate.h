@@ -258,6 +258,10 @@ int b200v_last_nccl_error(void);
 int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                                int warmup, int iters, b200v_ar_row *rows, int max_rows, int *nrows);
 int b200v_last_driver_error(void);
+/* Which kernel (B200V_AR_ALGO_*) the hand-written all-reduce uses for a message of `bytes` bytes
+ * over `nranks` GPUs, given the environment (B200V_NVLS_ALGO, B200V_NVLS_ONESHOT_MAX).  Host logic
+ * only: touches no device, so it also runs where there is none. */
+int b200v_nvls_algo_for(int nranks, size_t bytes);
 
 /* One-process-per-GPU form of the same probe.  Every rank calls it with the same `rendezvous`
  * string — the name of an abstract-namespace Unix socket on which rank 0 hands the multicast

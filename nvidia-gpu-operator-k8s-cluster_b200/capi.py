@@ -90,6 +90,7 @@ SIGNATURES = {
     "b200v_last_nccl_error": (_i, []),
     "b200v_nvls_allreduce_probe": (_i, [_i, _P(_i), _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_last_driver_error": (_i, []),
+    "b200v_nvls_algo_for": (_i, [_i, _sz]),
     "b200v_nvls_allreduce_probe_rank": (_i, [_i, _i, _i, ctypes.c_char_p, _sz, _sz, _i, _i, _P(ArRow), _i, _P(_i)]),
     "b200v_ar_comm_create": (_i, [_i, _i, _i, ctypes.c_char_p, _P(_vp)]),
     "b200v_ar_comm_allreduce": (_i, [_vp, _vp, _sz, _vp]),
@@ -291,6 +292,11 @@ def allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20)
 
 
 E_UNSUPPORTED, E_DRIVER, E_TIMEOUT = -8, -9, -10
+
+
+def nvls_algo_for(nranks, nbytes):
+    """Name of the kernel the hand-written all-reduce picks (host logic only, no GPU needed)."""
+    return AR_ALGO_NAMES[_check(lib().b200v_nvls_algo_for(nranks, nbytes), "b200v_nvls_algo_for", allow=(1, 2, 3, 4))]
 
 
 def nvls_allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20):

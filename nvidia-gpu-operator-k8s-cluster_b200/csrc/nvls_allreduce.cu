@@ -1001,6 +1001,15 @@ using namespace b200v;
 
 extern "C" int b200v_last_driver_error(void) { return g_last_cu; }
 
+// Host logic only (no device is touched): the kernel the probes and the comm pick for a message.
+extern "C" int b200v_nvls_algo_for(int nranks, size_t bytes) {
+    if (nranks < 2 || bytes == 0) return B200V_E_BADARG;
+    NvlsTeam t;
+    t.nranks = nranks;
+    t.peers_mapped = nranks <= kMaxPeers;
+    return choose_algo(read_tuning(), t, (bytes + 15) / 16 * 16) + 1;
+}
+
 extern "C" int b200v_nvls_allreduce_probe(int ndev, const int *devs, size_t min_bytes, size_t max_bytes,
                                           int warmup, int iters, b200v_ar_row *rows, int max_rows,
                                           int *nrows) {

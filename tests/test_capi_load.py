@@ -104,3 +104,27 @@ def test_product_sources_do_not_reference_oracle():
                 if re.search(r"oracle[/.]|liboracle|import oracle|from oracle", text):
                     offenders.append(os.path.join(base, f))
     assert offenders == []
+
+
+def test_allreduce_kernel_choice_is_host_logic(capi, monkeypatch):
+    """The size/rank-count table of the hand-written all-reduce, and its
+    environment overrides, evaluated without any GPU."""
+    for var in ("B200V_NVLS_ALGO", "B200V_NVLS_ONESHOT_MAX"):
+        monkeypatch.delenv(var, raising=False)
+    KiB, MiB = 1 << 10, 1 << 20
+    assert capi.nvls_algo_for(2, 1 * KiB) == "oneshot" and capi.nvls_algo_for(2, 2 * MiB) == "oneshot"
+    assert capi.nvls_algo_for(2, 2 * MiB + 16) == "push" and capi.nvls_algo_for(2, 1 << 30) == "push"
+    assert capi.nvls_algo_for(4, 1 * MiB) == "oneshot" and capi.nvls_algo_for(4, 1 * MiB + 16) == "push"
+    assert capi.nvls_algo_for(8, 512 * KiB) == "oneshot" and capi.nvls_algo_for(8, 512 * KiB + 16) == "multimem"
+    assert capi.nvls_algo_for(8, 1 << 30) == "multimem"
+    assert capi.nvls_algo_for(3, 1 << 30) == "multimem"          # peer kernels are built for 2, 4 and 8
+    assert capi.nvls_algo_for(16, 1 << 30) == "multimem"         # more ranks than peer mappings
+    monkeypatch.setenv("B200V_NVLS_ALGO", "p2p")
+    assert capi.nvls_algo_for(4, 1 * KiB) == "p2p" and capi.nvls_algo_for(3, 1 * KiB) == "multimem"
+    monkeypatch.setenv("B200V_NVLS_ALGO", "oneshot")
+    assert capi.nvls_algo_for(8, 4 * MiB) == "oneshot" and capi.nvls_algo_for(8, 4 * MiB + 16) == "multimem"
+    monkeypatch.delenv("B200V_NVLS_ALGO")
+    monkeypatch.setenv("B200V_NVLS_ONESHOT_MAX", str(64 * KiB))
+    assert capi.nvls_algo_for(2, 64 * KiB) == "oneshot" and capi.nvls_algo_for(2, 128 * KiB) == "push"
+    with pytest.raises(capi.B200VError):
+        capi.nvls_algo_for(1, 1024)

@@ -87,3 +87,26 @@ def test_concurrent_calls_from_threads(capi, oracle, gpu):
         t.join()
     assert not errors, errors
     assert len(results) == len(threads) and all(results.values())
+
+
+@pytest.mark.parametrize("policy", ["pinned", "wc", "thp"])
+def test_host_alloc_policies_give_the_same_bytes(capi, oracle, gpu, policy, monkeypatch):
+    """b200v_host_alloc_ex under each B200V_HOST_POLICY: inputs flagged write-only (they may come
+    back as write-combined memory, which the CPU only writes here), the output readable, the result
+    identical to the oracle's, and every block released by b200v_host_free."""
+    monkeypatch.setenv("B200V_HOST_POLICY", policy)
+    n = (1 << 22) + 77
+    a = oracle.fill_hash(n, 0x51, threads=4)
+    b = oracle.fill_hash(n, 0x52, threads=4)
+    ha, hb = capi.PinnedArray(n, write_only=True), capi.PinnedArray(n, write_only=True)
+    hc = capi.PinnedArray(n)
+    try:
+        ha.array[:] = a                              # CPU writes only
+        hb.array[:] = b
+        hc.array[:] = np.nan
+        t = capi.vectoradd(ha.array, hb.array, hc.array, n)
+        assert hc.array.tobytes() == oracle.vadd(a, b, threads=4).tobytes()
+        assert t.chunks >= 1 and t.kernel_launches == t.chunks
+    finally:
+        for h in (ha, hb, hc):
+            h.close()
