@@ -764,9 +764,9 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
     // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
     // latency-bound.  Measured crossovers (profiles/README.md): 2 MiB at 2 GPUs (18.5 vs 23.3 us;
-    // at 4 MiB 28.3 vs 25.7 us), 1 MiB at 4, 512 KiB at 8 where the traffic is 8x.
-    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max
-                             : (n == 2 ? (size_t)2 << 20 : n <= 4 ? (size_t)1 << 20 : (size_t)512 << 10);
+    // at 4 MiB 28.3 vs 25.7 us), 1 MiB at 4 and at 8 (8 GPUs: 512 KiB 16.0 vs 22.0 us, 1 MiB 22.6 vs
+    // 23.1 us, 2 MiB 34.9 vs 25.4 us).
+    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n == 2 ? (size_t)2 << 20 : (size_t)1 << 20);
     if (bytes <= oneshot_max) return ALGO_ONESHOT;
     // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
     // 4 GPUs the switch-side reduction moves fewer bytes per GPU.  (Measured: profiles/README.md.)

@@ -105,6 +105,48 @@ def test_nvls_comm_allreduce_matches_the_oracle(capi, gpu, oracle, algo, monkeyp
     _reduce_and_compare(make, nranks, oracle, SIZES[:3], repeats=3)
 
 
+@pytest.mark.parametrize("algo", ["push", "p2p"])
+def test_peer_kernels_add_in_rank_order(capi, gpu, algo, monkeypatch):
+    """Arbitrary floats, where the order of additions shows: the two peer kernels promise the
+    sequential sum over ranks 0..n-1 (one owner per slice adds in rank order and broadcasts), so
+    every rank must hold exactly the bytes of that fp32 sum."""
+    import torch
+    nranks = _nranks(gpu)
+    if nranks < 2:
+        pytest.skip("needs at least two GPUs")
+    monkeypatch.setenv("B200V_NVLS_ALGO", algo)
+    n = (1 << 20) + 37
+    rng = np.random.default_rng(2024)
+    inputs = [(rng.standard_normal(n) * 10.0 ** rng.integers(-3, 4, n)).astype(np.float32) for _ in range(nranks)]
+    want = inputs[0].copy()
+    for r in range(1, nranks):
+        want = want + inputs[r]                          # fp32, rank order
+    got = [None] * nranks
+    name = "b200v-order-%d-%s" % (os.getpid(), algo)
+
+    def rank_fn(r):
+        torch.cuda.set_device(r)
+        try:
+            comm = capi.NvlsComm(r, r, nranks, name, 4 * n + 64)
+        except capi.B200VError as e:
+            if e.code == capi.E_UNSUPPORTED:
+                return
+            raise
+        try:
+            buf = torch.from_numpy(inputs[r]).cuda(r)
+            comm.allreduce(buf.data_ptr(), n, stream=torch.cuda.current_stream(r).cuda_stream)
+            torch.cuda.synchronize(r)
+            comm.check()
+            got[r] = buf.cpu().numpy()
+        finally:
+            comm.close()
+    _run_ranks(nranks, rank_fn)
+    if any(g is None for g in got):
+        pytest.skip("no multicast support on this box")
+    for r in range(nranks):
+        assert got[r].tobytes() == want.tobytes(), "rank %d" % r
+
+
 def test_nvls_comm_rejects_what_it_cannot_hold(capi, gpu):
     import torch
     with pytest.raises(capi.B200VError) as ei:
