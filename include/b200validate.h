@@ -110,6 +110,7 @@ typedef struct b200v_ar_row {
 #define B200V_AR_ALGO_P2P      2   /* peer loads + peer stores */
 #define B200V_AR_ALGO_PUSH     3   /* two phases of peer stores */
 #define B200V_AR_ALGO_ONESHOT  4   /* every GPU reduces the whole (small) vector itself */
+#define B200V_AR_ALGO_HYBRID   5   /* one grid: part of the vector through the switch, the rest by peer stores */
 
 /* ---- library / device queries ----------------------------------------------------------------- */
 

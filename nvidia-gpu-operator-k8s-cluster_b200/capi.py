@@ -51,7 +51,7 @@ class ArRow(ctypes.Structure):
                 ("mismatches", ctypes.c_uint64), ("nccl_result", ctypes.c_int), ("algo", ctypes.c_int)]
 
 
-AR_ALGO_NAMES = {0: "nccl", 1: "multimem", 2: "p2p", 3: "push", 4: "oneshot"}
+AR_ALGO_NAMES = {0: "nccl", 1: "multimem", 2: "p2p", 3: "push", 4: "oneshot", 5: "hybrid"}
 
 
 class B200VError(RuntimeError):
@@ -296,7 +296,7 @@ E_UNSUPPORTED, E_DRIVER, E_TIMEOUT = -8, -9, -10
 
 def nvls_algo_for(nranks, nbytes):
     """Name of the kernel the hand-written all-reduce picks (host logic only, no GPU needed)."""
-    return AR_ALGO_NAMES[_check(lib().b200v_nvls_algo_for(nranks, nbytes), "b200v_nvls_algo_for", allow=(1, 2, 3, 4))]
+    return AR_ALGO_NAMES[_check(lib().b200v_nvls_algo_for(nranks, nbytes), "b200v_nvls_algo_for", allow=(1, 2, 3, 4, 5))]
 
 
 def nvls_allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20):

@@ -209,13 +209,14 @@ __device__ __forceinline__ void add4(float4 &s, const float4 &v) {
     s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
 }
 
-// ---- multimem, two-shot: in-place sum of n4 float4 vectors in the data region ------------------------
+// ---- multimem, two-shot: in-place sum of `len` float4 vectors starting at vector `vbase` of the data
+// region.  `cta` of `nctas` is this CTA's share of the work; the barrier flag and the epoch word
+// are always the ones of blockIdx.x, so several bodies can share one grid (hybrid kernel below).
 template <int UNROLL>
-__global__ void __launch_bounds__(kThreads)
-nvls_allreduce_kernel(ArArgs a, size_t n4) {
+__device__ __forceinline__ void multimem_body(const ArArgs &a, size_t vbase, size_t len, unsigned cta, unsigned nctas) {
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
-    float *mc = reinterpret_cast<float *>(a.mc_base + a.data_off);
+    float *mc = reinterpret_cast<float *>(a.mc_base + a.data_off) + 4 * vbase;
     const unsigned epoch = load_epoch(a);
     const unsigned nr = (unsigned)a.nranks;
 
@@ -225,13 +226,13 @@ nvls_allreduce_kernel(ArArgs a, size_t n4) {
         if (threadIdx.x == 0) atomicExch(a.err, 1);
         return;
     }
-    const size_t per = (n4 + (size_t)nr - 1) / (size_t)nr;
-    const size_t lo = per * (size_t)a.rank < n4 ? per * (size_t)a.rank : n4;
-    const size_t hi = lo + per < n4 ? lo + per : n4;
-    // CTA b walks tiles b, b+grid, ... of its GPU's slice; a tile is UNROLL x kThreads float4s, and a
+    const size_t per = (len + (size_t)nr - 1) / (size_t)nr;
+    const size_t lo = per * (size_t)a.rank < len ? per * (size_t)a.rank : len;
+    const size_t hi = lo + per < len ? lo + per : len;
+    // CTA b walks tiles b, b+nctas, ... of its GPU's slice; a tile is UNROLL x kThreads float4s, and a
     // thread issues all UNROLL switch-side reductions before the first broadcast store.
     constexpr size_t TILE = (size_t)UNROLL * kThreads;
-    for (size_t t0 = lo + (size_t)blockIdx.x * TILE; t0 < hi; t0 += (size_t)gridDim.x * TILE) {
+    for (size_t t0 = lo + (size_t)cta * TILE; t0 < hi; t0 += (size_t)nctas * TILE) {
         float4 acc[UNROLL];
         if (t0 + TILE <= hi) {
 #pragma unroll
@@ -252,6 +253,12 @@ nvls_allreduce_kernel(ArArgs a, size_t n4) {
         if (threadIdx.x == 0) atomicExch(a.err, 2);
     }
     store_epoch(a, epoch + 2u * nr);
+}
+
+template <int UNROLL>
+__global__ void __launch_bounds__(kThreads)
+nvls_allreduce_kernel(const __grid_constant__ ArArgs a, size_t n4) {
+    multimem_body<UNROLL>(a, 0, n4, blockIdx.x, gridDim.x);
 }
 
 // ---- one-shot: out[v] = sum over GPUs of in[v], every GPU computing the whole vector ------------------
@@ -340,22 +347,21 @@ p2p_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ P
 __device__ __forceinline__ int push_slot(int s, int p) { return s < p ? s : s - 1; }
 
 template <int NR, int UNROLL>
-__global__ void __launch_bounds__(kThreads)
-push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ PeerPtrs data,
-                      const __grid_constant__ PeerPtrs scratch, size_t n4) {
+__device__ __forceinline__ void push_body(const ArArgs &a, const PeerPtrs &data, const PeerPtrs &scratch, size_t vbase,
+                                          size_t len, unsigned cta, unsigned nctas) {
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
     const unsigned epoch = load_epoch(a);
     const int rank = a.rank;
-    const size_t per = (n4 + (size_t)NR - 1) / (size_t)NR;
-    const float *mine = data.p[rank];
+    const size_t per = (len + (size_t)NR - 1) / (size_t)NR;
+    const float *mine = data.p[rank] + 4 * vbase;
     constexpr size_t TILE = (size_t)UNROLL * kThreads;
 
     // Phase 1 needs no opening barrier: it reads only this GPU's own input (complete, by stream
     // order) and writes only peers' scratch, which every GPU finished reading before anyone could
     // leave the previous launch.  CTA b handles the same offsets of every slice in both phases,
     // so the per-CTA barrier below is all the ordering phase 2 needs.
-    for (size_t t0 = (size_t)blockIdx.x * TILE; t0 < per; t0 += (size_t)gridDim.x * TILE) {
+    for (size_t t0 = (size_t)cta * TILE; t0 < per; t0 += (size_t)nctas * TILE) {
         float4 v[UNROLL][NR - 1];
 #pragma unroll
         for (int j = 0; j < UNROLL; ++j) {
@@ -364,7 +370,7 @@ push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ 
             for (int q = 1; q < NR; ++q) {
                 const int p = (rank + q) % NR;
                 const size_t idx = (size_t)p * per + o;
-                if (o < per && idx < n4) v[j][q - 1] = ld_f4<false>(mine + 4 * idx);
+                if (o < per && idx < len) v[j][q - 1] = ld_f4<false>(mine + 4 * idx);
             }
         }
 #pragma unroll
@@ -374,7 +380,7 @@ push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ 
             for (int q = 1; q < NR; ++q) {
                 const int p = (rank + q) % NR;
                 const size_t idx = (size_t)p * per + o;
-                if (o < per && idx < n4)
+                if (o < per && idx < len)
                     st_f4<true>(scratch.p[p] + 4 * ((size_t)push_slot(rank, p) * per + o), v[j][q - 1]);
             }
         }
@@ -385,13 +391,13 @@ push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ 
     }
     // Phase 2: own slice + the N-1 copies that arrived, added in rank order, stored to every GPU.
     const float *inbox = scratch.p[rank];
-    for (size_t t0 = (size_t)blockIdx.x * TILE; t0 < per; t0 += (size_t)gridDim.x * TILE) {
+    for (size_t t0 = (size_t)cta * TILE; t0 < per; t0 += (size_t)nctas * TILE) {
         float4 in[UNROLL][NR];
 #pragma unroll
         for (int j = 0; j < UNROLL; ++j) {
             const size_t o = t0 + (size_t)j * kThreads + threadIdx.x;
             const size_t idx = (size_t)rank * per + o;
-            if (o < per && idx < n4) {
+            if (o < per && idx < len) {
 #pragma unroll
                 for (int s = 0; s < NR; ++s)
                     in[j][s] = s == rank ? ld_f4<false>(mine + 4 * idx)
@@ -402,12 +408,12 @@ push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ 
         for (int j = 0; j < UNROLL; ++j) {
             const size_t o = t0 + (size_t)j * kThreads + threadIdx.x;
             const size_t idx = (size_t)rank * per + o;
-            if (o < per && idx < n4) {
+            if (o < per && idx < len) {
                 float4 s = in[j][0];
 #pragma unroll
                 for (int r = 1; r < NR; ++r) add4(s, in[j][r]);
 #pragma unroll
-                for (int p = 0; p < NR; ++p) st_f4<true>(data.p[p] + 4 * idx, s);
+                for (int p = 0; p < NR; ++p) st_f4<true>(data.p[p] + 4 * (vbase + idx), s);
             }
         }
     }
@@ -415,6 +421,27 @@ push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ 
         if (threadIdx.x == 0) atomicExch(a.err, 2);
     }
     store_epoch(a, epoch + 2u * (unsigned)NR);
+}
+
+template <int NR, int UNROLL>
+__global__ void __launch_bounds__(kThreads)
+push_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ PeerPtrs data,
+                      const __grid_constant__ PeerPtrs scratch, size_t n4) {
+    push_body<NR, UNROLL>(a, data, scratch, 0, n4, blockIdx.x, gridDim.x);
+}
+
+// ---- hybrid: both of the above in one grid, on disjoint parts of the vector ----------------------------
+// The switch-side reduction tops out near 540-570 GB/s per direction per GPU and SM-issued stores
+// near 700, and neither fills the link alone.  CTAs [0, mm_ctas) reduce vectors [0, m4) through the
+// switch while the remaining CTAs push-reduce vectors [m4, n4): two independent all-reduces that
+// share one launch and overlap on the wire.  Every CTA keeps its own barrier flag (blockIdx.x),
+// so the two halves never wait on each other.
+template <int NR, int UM, int UP>
+__global__ void __launch_bounds__(kThreads)
+hybrid_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ PeerPtrs data,
+                        const __grid_constant__ PeerPtrs scratch, size_t n4, size_t m4, unsigned mm_ctas) {
+    if (blockIdx.x < mm_ctas) multimem_body<UM>(a, 0, m4, blockIdx.x, mm_ctas);
+    else push_body<NR, UP>(a, data, scratch, m4, n4 - m4, blockIdx.x - mm_ctas, gridDim.x - mm_ctas);
 }
 
 // ---- host side ------------------------------------------------------------------------------------------
@@ -709,13 +736,14 @@ int grid_fill(const NvlsRank &r, size_t n) {
 
 // ---- algorithm choice and launch ------------------------------------------------------------------------
 
-enum Algo { ALGO_MULTIMEM = 0, ALGO_P2P = 1, ALGO_PUSH = 2, ALGO_ONESHOT = 3 };
+enum Algo { ALGO_MULTIMEM = 0, ALGO_P2P = 1, ALGO_PUSH = 2, ALGO_ONESHOT = 3, ALGO_HYBRID = 4 };
 
 const char *algo_name(int a) {
     switch (a) {
     case ALGO_MULTIMEM: return "multimem";
     case ALGO_P2P: return "p2p";
     case ALGO_PUSH: return "push";
+    case ALGO_HYBRID: return "hybrid";
     default: return "oneshot";
     }
 }
@@ -725,6 +753,8 @@ struct Tuning {
     int ctas = 0;                    // B200V_NVLS_CTAS (0 = per-algorithm default)
     int unroll = 0;                  // B200V_NVLS_UNROLL (0 = per-algorithm default)
     size_t oneshot_max = 0;          // B200V_NVLS_ONESHOT_MAX bytes (messages up to this go one-shot)
+    int hybrid_pct = 0;              // B200V_NVLS_HYBRID_PCT: share of the vector reduced in the switch (0 = default)
+    int hybrid_mm_ctas = 0;          // B200V_NVLS_HYBRID_MM_CTAS: CTAs on the switch-side part (0 = default)
     unsigned long long timeout_ns = 2000ull * 1000000ull;
 };
 
@@ -735,6 +765,15 @@ Tuning read_tuning() {
         else if (!std::strcmp(e, "p2p")) t.forced = ALGO_P2P;
         else if (!std::strcmp(e, "push")) t.forced = ALGO_PUSH;
         else if (!std::strcmp(e, "oneshot")) t.forced = ALGO_ONESHOT;
+        else if (!std::strcmp(e, "hybrid")) t.forced = ALGO_HYBRID;
+    }
+    if (const char *e = std::getenv("B200V_NVLS_HYBRID_PCT")) {
+        const int v = std::atoi(e);
+        if (v >= 1 && v <= 99) t.hybrid_pct = v;
+    }
+    if (const char *e = std::getenv("B200V_NVLS_HYBRID_MM_CTAS")) {
+        const int v = std::atoi(e);
+        if (v >= 1 && v <= 128) t.hybrid_mm_ctas = v;
     }
     if (const char *e = std::getenv("B200V_NVLS_CTAS")) {
         const int v = std::atoi(e);
@@ -762,6 +801,7 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_MULTIMEM) return ALGO_MULTIMEM;
     if (tn.forced == ALGO_P2P) return peers ? ALGO_P2P : ALGO_MULTIMEM;
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
+    if (tn.forced == ALGO_HYBRID) return (peers && n >= 4) ? ALGO_HYBRID : ALGO_MULTIMEM;
     // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
     // latency-bound.  Measured crossovers (profiles/README.md): 2 MiB at 2 GPUs (18.5 vs 23.3 us;
     // at 4 MiB 28.3 vs 25.7 us), 1 MiB at 4 and at 8 (8 GPUs: 512 KiB 16.0 vs 22.0 us, 1 MiB 22.6 vs
@@ -837,6 +877,21 @@ int launch_allreduce(const Tuning &tn, NvlsTeam &t, NvlsRank &r, int algo, size_
             auto kern = u == 2 ? push_allreduce_kernel<8, 2> : push_allreduce_kernel<8, 1>;
             kern<<<ctas, kThreads, 0, st>>>(a, data, scratch, n4);
         }
+        break;
+    }
+    case ALGO_HYBRID: {
+        const int pct = tn.hybrid_pct ? tn.hybrid_pct : 83;
+        const unsigned mm = (unsigned)std::min(tn.hybrid_mm_ctas ? tn.hybrid_mm_ctas : 16, r.sm_count / 2);
+        ctas = tn.ctas ? std::max(tn.ctas, (int)mm + 1) : r.sm_count;
+        // the switch-side part is a whole number of (ranks x 512-vector) units so both parts stay aligned
+        size_t m4 = n4 * (size_t)pct / 100;
+        m4 -= m4 % ((size_t)n * kThreads);
+        if (m4 == 0 || m4 >= n4) {            // too small to split: all of it through the switch
+            nvls_allreduce_kernel<4><<<(int)mm, kThreads, 0, st>>>(a, n4);
+            break;
+        }
+        if (n == 4) hybrid_allreduce_kernel<4, 4, 2><<<ctas, kThreads, 0, st>>>(a, data, scratch, n4, m4, mm);
+        else hybrid_allreduce_kernel<8, 4, 1><<<ctas, kThreads, 0, st>>>(a, data, scratch, n4, m4, mm);
         break;
     }
     default: {

@@ -81,7 +81,7 @@ def test_nccl_comm_allreduce_matches_the_oracle(capi, gpu, oracle):
     _reduce_and_compare(lambda r: capi.ArComm(r, r, nranks, uid), nranks, oracle, SIZES[:3], repeats=3)
 
 
-@pytest.mark.parametrize("algo", ["auto", "multimem", "oneshot", "p2p", "push"])
+@pytest.mark.parametrize("algo", ["auto", "multimem", "oneshot", "p2p", "push", "hybrid"])
 def test_nvls_comm_allreduce_matches_the_oracle(capi, gpu, oracle, algo, monkeypatch):
     nranks = _nranks(gpu)
     if nranks < 2:

@@ -29,7 +29,7 @@ def test_nvls_allreduce_ragged_slices_and_both_algorithms(capi, gpu, monkeypatch
     if gpu < 2:
         pytest.skip("needs at least two GPUs")
     ranks = 2 if gpu < 4 else (4 if gpu < 8 else 8)
-    for algo in ("multimem", "p2p", "push", "oneshot"):
+    for algo in ("multimem", "p2p", "push", "oneshot", "hybrid"):
         monkeypatch.setenv("B200V_NVLS_ALGO", algo)
         try:
             rows = capi.nvls_allreduce_probe(list(range(ranks)), min_bytes=63 * 16, max_bytes=63 * 16 << 12,
