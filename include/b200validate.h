@@ -252,7 +252,7 @@ int b200v_last_nccl_error(void);
  * depends on the message size and the GPU count (row.algo says which): one-shot
  * multimem.ld_reduce for small messages, two phases of peer stores for large messages on 2 and 4
  * GPUs, multimem.ld_reduce + multimem.st (reduction inside the NVSwitch) otherwise;
- * B200V_NVLS_ALGO=multimem|p2p|push|oneshot forces one.  Every size is checked twice, before the
+ * B200V_NVLS_ALGO=multimem|p2p|push|oneshot|hybrid forces one.  Every size is checked twice, before the
  * timed launches and again after them.  Single process, one host thread per GPU, 2 <= ndev
  * distinct devices (a multicast object cannot be made for one), sizes are multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast support,
  * B200V_E_TIMEOUT if a peer GPU never reaches a barrier (bounded spin, default 2 s). */
