@@ -62,7 +62,7 @@ def test_recorded_b200_lines_keep_the_contract(name):
         assert d["allreduce"]["bit_exact"] is True
 
 
-@pytest.mark.parametrize("name", ["r02_bench_n1.json", "r02_bench_n8.json"])
+@pytest.mark.parametrize("name", ["r02_bench_n1.json", "r02_bench_n2.json", "r02_bench_n4.json", "r02_bench_n8.json"])
 def test_round2_lines_carry_what_the_verdict_asked_for(name):
     with open(os.path.join(ROOT, "profiles", name)) as f:
         d = json.loads(f.read().strip())
