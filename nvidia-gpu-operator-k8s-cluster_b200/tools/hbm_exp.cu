@@ -115,6 +115,41 @@ int main(int argc, char **argv) {
         }
         return 0;
     }
+    if (mode == "gap") {
+        // What separates two back-to-back launches of the default kernel: K launches on a stream, the
+        // same K as nodes of one CUDA graph, timed as a whole; per-launch time against ncu's 445.7 us.
+        const int K = 200;
+        ew_fn fn = (ew_fn)ew_tile_kernel<B200V_OP_VECTORADD, 8, 1, 1024, LD_PLAIN, ST_PLAIN, 2>;
+        const unsigned grid = (unsigned)(n / 8192);
+        cudaStream_t st;
+        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        for (int i = 0; i < 10; ++i) fn<<<grid, 1024, 0, st>>>(d0, x0, y0, 3.0f, n);
+        for (int rep = 0; rep < 3; ++rep) {
+            CK(cudaEventRecord(e0, st));
+            for (int i = 0; i < K; ++i) fn<<<grid, 1024, 0, st>>>(d0, x0, y0, 3.0f, n);
+            CK(cudaEventRecord(e1, st));
+            CK(cudaStreamSynchronize(st));
+            float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+            std::printf("gap,vectoradd,stream_x%d,%.5f,%.1f,0\n", K, ms / K, 12.0 * n / (ms / K) / 1e6);
+        }
+        cudaGraph_t g; cudaGraphExec_t ge;
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        for (int i = 0; i < K; ++i) fn<<<grid, 1024, 0, st>>>(d0, x0, y0, 3.0f, n);
+        CK(cudaStreamEndCapture(st, &g));
+        CK(cudaGraphInstantiate(&ge, g, 0));
+        CK(cudaGraphLaunch(ge, st)); CK(cudaStreamSynchronize(st));
+        for (int rep = 0; rep < 3; ++rep) {
+            CK(cudaEventRecord(e0, st));
+            CK(cudaGraphLaunch(ge, st));
+            CK(cudaEventRecord(e1, st));
+            CK(cudaStreamSynchronize(st));
+            float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+            std::printf("gap,vectoradd,graph_x%d,%.5f,%.1f,0\n", K, ms / K, 12.0 * n / (ms / K) / 1e6);
+        }
+        return 0;
+    }
     // burst: shapes for the 1R:1W ops
     struct Shape { const char *name; ew_fn copy, scale; int block; size_t tile; };
 #define TILE_SHAPE(V, U, B, M) {"tile_v" #V "_u" #U "_b" #B, ew_tile_kernel<B200V_OP_COPY, V, U, B, LD_PLAIN, ST_PLAIN, M>, \
