@@ -141,7 +141,9 @@ __device__ __forceinline__ bool gpu_barrier(unsigned *mc_flag, unsigned *uc_flag
     __shared__ int ok_s;
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence_system();
+        // The CTA's stores were ordered before this point by the bar.sync above; the release on the
+        // arrival (a system-scope fence followed by the reduction) publishes them, cumulatively,
+        // before any peer can observe the count.  No separate __threadfence_system() is needed.
         asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc_flag), "r"(1u) : "memory");
         const unsigned long long t0 = now_ns();
         int ok = 1;
@@ -156,6 +158,35 @@ __device__ __forceinline__ bool gpu_barrier(unsigned *mc_flag, unsigned *uc_flag
     }
     __syncthreads();
     return ok_s != 0;
+}
+
+// Opening barrier of a kernel that has not written anything yet (its inputs were produced by earlier
+// work on the stream, complete at the kernel boundary): the arrival is sent first, with nothing to
+// wait for on this side, and the CTA's epoch word is fetched while it is in flight.  Returns the
+// epoch the CTA started from through *epoch_out; false on timeout.
+__device__ __forceinline__ bool gpu_barrier_open(const unsigned *epochs, unsigned *mc_flag, unsigned *uc_flag,
+                                                 unsigned nranks, unsigned long long timeout_ns, unsigned *epoch_out) {
+    __shared__ int ok_o;
+    __shared__ unsigned epoch_o;
+    if (threadIdx.x == 0) {
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc_flag), "r"(1u) : "memory");
+        const unsigned epoch = epochs[blockIdx.x];
+        const unsigned target = epoch + nranks;
+        const unsigned long long t0 = now_ns();
+        int ok = 1;
+        unsigned polls = 0;
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(uc_flag) : "memory");
+            if ((int)(v - target) >= 0) break;
+            if ((++polls & 1023u) == 0 && now_ns() - t0 > timeout_ns) { ok = 0; break; }
+        }
+        ok_o = ok;
+        epoch_o = epoch;
+    }
+    __syncthreads();
+    *epoch_out = epoch_o;
+    return ok_o != 0;
 }
 
 // The barrier count this CTA index has consumed so far (same value on every GPU, because every
@@ -217,12 +248,12 @@ __device__ __forceinline__ void multimem_body(const ArArgs &a, size_t vbase, siz
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
     float *mc = reinterpret_cast<float *>(a.mc_base + a.data_off) + 4 * vbase;
-    const unsigned epoch = load_epoch(a);
     const unsigned nr = (unsigned)a.nranks;
 
     // (1) every GPU has entered this kernel, so every GPU's input (produced earlier on its stream)
     //     is complete and visible
-    if (!gpu_barrier(mc_flag, uc_flag, epoch + nr, a.timeout_ns)) {
+    unsigned epoch;
+    if (!gpu_barrier_open(a.epochs, mc_flag, uc_flag, nr, a.timeout_ns, &epoch)) {
         if (threadIdx.x == 0) atomicExch(a.err, 1);
         return;
     }
@@ -269,30 +300,14 @@ oneshot_allreduce_kernel(ArArgs a, size_t in_off, float *__restrict__ out, size_
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
     const float *mc = reinterpret_cast<const float *>(a.mc_base + in_off);
-    // The lean form of gpu_barrier, for the latency-bound case.  This kernel has written nothing
-    // before its only barrier — the input slot was filled by earlier work on the stream, which is
-    // complete and in this GPU's L2 at the kernel boundary — so the arrival needs no system-wide
-    // fence of its own: the release on the reduction is enough.  The arrival is sent first and the
-    // CTA's epoch word is fetched while it is in flight.
-    __shared__ int ok_s;
-    if (threadIdx.x == 0) {
-        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc_flag), "r"(1u) : "memory");
-        const unsigned target = a.epochs[blockIdx.x] + (unsigned)a.nranks;
-        const unsigned long long t0 = now_ns();
-        int ok = 1;
-        unsigned polls = 0;
-        for (;;) {
-            unsigned v;
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(uc_flag) : "memory");
-            if ((int)(v - target) >= 0) break;
-            if ((++polls & 1023u) == 0 && now_ns() - t0 > a.timeout_ns) { ok = 0; break; }
-        }
-        a.epochs[blockIdx.x] = target;
-        if (!ok) atomicExch(a.err, 1);
-        ok_s = ok;
+    // gpu_barrier_open: this kernel has written nothing before its only barrier.
+    unsigned epoch;
+    const bool ok = gpu_barrier_open(a.epochs, mc_flag, uc_flag, (unsigned)a.nranks, a.timeout_ns, &epoch);
+    store_epoch(a, epoch + (unsigned)a.nranks);
+    if (!ok) {
+        if (threadIdx.x == 0) atomicExch(a.err, 1);
+        return;
     }
-    __syncthreads();
-    if (!ok_s) return;
     for (size_t v = (size_t)blockIdx.x * kThreads + threadIdx.x; v < n4; v += (size_t)gridDim.x * kThreads)
         st_f4<false>(out + 4 * v, mm_ld_reduce(mc + 4 * v));
 }
@@ -305,8 +320,8 @@ __global__ void __launch_bounds__(kThreads)
 p2p_allreduce_kernel(const __grid_constant__ ArArgs a, const __grid_constant__ PeerPtrs data, size_t n4) {
     unsigned *mc_flag = reinterpret_cast<unsigned *>(a.mc_base) + blockIdx.x;
     unsigned *uc_flag = reinterpret_cast<unsigned *>(a.uc_base) + blockIdx.x;
-    const unsigned epoch = load_epoch(a);
-    if (!gpu_barrier(mc_flag, uc_flag, epoch + (unsigned)NR, a.timeout_ns)) {
+    unsigned epoch;
+    if (!gpu_barrier_open(a.epochs, mc_flag, uc_flag, (unsigned)NR, a.timeout_ns, &epoch)) {
         if (threadIdx.x == 0) atomicExch(a.err, 1);
         return;
     }
