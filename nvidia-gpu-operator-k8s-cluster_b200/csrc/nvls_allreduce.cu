@@ -818,15 +818,18 @@ int choose_algo(const Tuning &tn, const NvlsTeam &t, size_t bytes) {
     if (tn.forced == ALGO_PUSH) return peers ? ALGO_PUSH : ALGO_MULTIMEM;
     if (tn.forced == ALGO_HYBRID) return (peers && n >= 4) ? ALGO_HYBRID : ALGO_MULTIMEM;
     // One-shot moves N times the bytes but saves a barrier and a pass: it wins while the message is
-    // latency-bound.  Measured crossovers (profiles/README.md): 2 MiB at 2 GPUs (18.5 vs 23.3 us;
-    // at 4 MiB 28.3 vs 25.7 us), 1 MiB at 4 and at 8 (8 GPUs: 512 KiB 16.0 vs 22.0 us, 1 MiB 22.6 vs
-    // 23.1 us, 2 MiB 34.9 vs 25.4 us).
-    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max : (n == 2 ? (size_t)2 << 20 : (size_t)1 << 20);
+    // latency-bound.  Measured crossovers with the lean barriers (profiles/README.md, us per call):
+    //   2 GPUs  1 MiB 13.9 vs 15.9 (push), 2 MiB 18.5 vs 19.2, 4 MiB 28.3 vs 20.6   -> 2 MiB
+    //   4 GPUs  1 MiB 16.4 vs 17.5 (multimem), 2 MiB 23.3 vs 19.5                   -> 1 MiB
+    //   8 GPUs  512 KiB 16.0 vs 16.9 (multimem), 1 MiB 22.4 vs 18.0                 -> 512 KiB
+    const size_t oneshot_max = tn.oneshot_max ? tn.oneshot_max
+                             : (n == 2 ? (size_t)2 << 20 : n <= 4 ? (size_t)1 << 20 : (size_t)512 << 10);
     if (bytes <= oneshot_max) return ALGO_ONESHOT;
-    // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer kernels win; from
-    // 4 GPUs the switch-side reduction moves fewer bytes per GPU.  (Measured: profiles/README.md.)
+    // Large messages: with 2 GPUs the switch has nothing to reduce, so the peer-store kernel wins
+    // (694 vs 408 GB/s at 1 GiB).  From 4 GPUs the switch-side reduction moves fewer bytes per GPU:
+    // at 4 it ties push at 1 GiB (680-688 both) and is 2-6 % ahead from 2 to 16 MiB; at 8 it is far
+    // ahead (842 GB/s).
     if (n == 2 && peers) return ALGO_PUSH;
-    if (n == 4 && peers) return ALGO_PUSH;
     return ALGO_MULTIMEM;
 }
 

@@ -114,8 +114,9 @@ def test_allreduce_kernel_choice_is_host_logic(capi, monkeypatch):
     KiB, MiB = 1 << 10, 1 << 20
     assert capi.nvls_algo_for(2, 1 * KiB) == "oneshot" and capi.nvls_algo_for(2, 2 * MiB) == "oneshot"
     assert capi.nvls_algo_for(2, 2 * MiB + 16) == "push" and capi.nvls_algo_for(2, 1 << 30) == "push"
-    assert capi.nvls_algo_for(4, 1 * MiB) == "oneshot" and capi.nvls_algo_for(4, 1 * MiB + 16) == "push"
-    assert capi.nvls_algo_for(8, 1 * MiB) == "oneshot" and capi.nvls_algo_for(8, 1 * MiB + 16) == "multimem"
+    assert capi.nvls_algo_for(4, 1 * MiB) == "oneshot" and capi.nvls_algo_for(4, 1 * MiB + 16) == "multimem"
+    assert capi.nvls_algo_for(4, 1 << 30) == "multimem"
+    assert capi.nvls_algo_for(8, 512 * KiB) == "oneshot" and capi.nvls_algo_for(8, 512 * KiB + 16) == "multimem"
     assert capi.nvls_algo_for(8, 1 << 30) == "multimem"
     assert capi.nvls_algo_for(3, 1 << 30) == "multimem"          # peer kernels are built for 2, 4 and 8
     assert capi.nvls_algo_for(16, 1 << 30) == "multimem"         # more ranks than peer mappings
