@@ -282,6 +282,7 @@ def _rows(rows, n):
 
 
 def allreduce_probe(devs, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20):
+    _settle_nccl()
     devs = list(devs)
     arr = (_i * len(devs))(*devs)
     rows = (ArRow * 64)()
@@ -321,7 +322,19 @@ def nvls_allreduce_probe_rank(dev, rank, nranks, rendezvous, min_bytes=1024, max
     return _rows(rows, n.value)
 
 
+def _settle_nccl():
+    """A process gets ONE libnccl.so.2: whichever is mapped first.  The library dlopen()s the
+    system's on first use; torch brings a newer one and fails to import if the older is already
+    there.  In a Python process (tests, bench.py) let torch map its copy first; the library then
+    finds it already loaded and uses it.  No torch, no problem: the system's is used."""
+    try:
+        import torch  # noqa: F401
+    except Exception:
+        pass
+
+
 def nccl_unique_id():
+    _settle_nccl()
     buf = ctypes.create_string_buffer(NCCL_UNIQUE_ID_BYTES)
     _check(lib().b200v_nccl_unique_id(buf), "b200v_nccl_unique_id")
     return buf.raw
@@ -329,6 +342,7 @@ def nccl_unique_id():
 
 def allreduce_probe_rank(dev, rank, nranks, uid, min_bytes=1024, max_bytes=1 << 30, warmup=5, iters=20):
     assert len(uid) == NCCL_UNIQUE_ID_BYTES
+    _settle_nccl()
     rows = (ArRow * 64)()
     n = _i()
     _check(lib().b200v_allreduce_probe_rank(dev, rank, nranks, uid, min_bytes, max_bytes, warmup, iters,
@@ -342,6 +356,7 @@ class ArComm:
 
     def __init__(self, dev, rank, nranks, uid):
         assert len(uid) == NCCL_UNIQUE_ID_BYTES
+        _settle_nccl()
         h = _vp()
         _check(lib().b200v_ar_comm_create(dev, rank, nranks, uid, ctypes.byref(h)), "b200v_ar_comm_create")
         self.h = h
@@ -380,6 +395,7 @@ class NvlsComm:
 
 
 def nccl_version():
+    _settle_nccl()
     v = _i()
     _check(lib().b200v_nccl_version(ctypes.byref(v)), "b200v_nccl_version")
     return v.value

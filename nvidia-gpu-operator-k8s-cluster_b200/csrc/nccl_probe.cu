@@ -51,8 +51,16 @@ bool sym(void *h, const char *name, F &out) {
 
 const NcclApi *nccl() {
     std::call_once(g_nccl_once, [] {
-        void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        // Order matters when the host process carries an NCCL of its own (a Python process with
+        // torch does): two builds share the soname libnccl.so.2, and whichever is mapped first is
+        // the one every later DT_NEEDED resolves to.  So: the library the caller names
+        // (B200V_NCCL_LIB), else one the process has already loaded, else the system's — and
+        // never RTLD_GLOBAL, every symbol is fetched from the handle.
+        void *h = nullptr;
+        if (const char *path = std::getenv("B200V_NCCL_LIB")) h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
         if (!h) return;
         NcclApi a;
         a.handle = h;
