@@ -249,9 +249,10 @@ int b200v_last_nccl_error(void);
 /* A second, hand-written NVLink probe (nothing upstream): the same sweep, input
  * pattern, bit-exact check and row format as b200v_allreduce_probe, but the all-reduce is one
  * sm_100a kernel per GPU over a CUDA multicast object and peer mappings.  Which kernel runs
- * depends on the message size and the GPU count (row.algo says which): one-shot
- * multimem.ld_reduce for small messages, two phases of peer stores for large messages on 2 and 4
- * GPUs, multimem.ld_reduce + multimem.st (reduction inside the NVSwitch) otherwise;
+ * depends on the message size and the GPU count (row.algo says which; b200v_nvls_algo_for
+ * answers without a GPU): one-shot multimem.ld_reduce for small messages (up to 2 MiB / 1 MiB /
+ * 512 KiB at 2 / 4 / 8 GPUs), two phases of peer stores for larger messages on 2 GPUs,
+ * multimem.ld_reduce + multimem.st (reduction inside the NVSwitch) from 4 GPUs;
  * B200V_NVLS_ALGO=multimem|p2p|push|oneshot|hybrid forces one.  Every size is checked twice, before the
  * timed launches and again after them.  Single process, one host thread per GPU, 2 <= ndev
  * distinct devices (a multicast object cannot be made for one), sizes are multiples of 16 bytes.  B200V_E_UNSUPPORTED when the GPUs or the driver have no multicast support,

@@ -7,7 +7,7 @@
 // on all GPUs", and mapped into every peer, so each GPU can also load from and store to any other
 // GPU's copy directly.  Four kernels share that memory (one launch per GPU per all-reduce):
 //
-//   multimem (two-shot, switch-side reduction; default from 4 GPUs, large messages)
+//   multimem (two-shot, switch-side reduction; default from 4 GPUs above the one-shot sizes)
 //       GPU r owns slice r.  multimem.ld_reduce.add.v4.f32 makes the NVSwitch read that offset from
 //       all N GPUs and return the sum; multimem.st.v4.f32 makes it write the sum back to all N.
 //       Per GPU about (1 + 1/N) S bytes each way instead of a ring's 2(N-1)/N S.
@@ -19,17 +19,21 @@
 //       call k+1 once every rank has finished reading in call k.
 //   p2p (pull + push, plain peer loads and stores)
 //       GPU r loads slice r from every GPU, adds in rank order, stores the sum to every GPU.
-//   push (two-phase, stores only)
+//   push (two-phase, stores only; default at 2 GPUs above the one-shot sizes)
 //       phase 1: every GPU stores its copy of slice p into GPU p's scratch (no loads cross NVLink,
 //       so nothing waits a round trip and no read requests compete with data); barrier;
 //       phase 2: GPU r adds its own slice r and the N-1 copies in its scratch, in rank order, and
 //       stores the sum to every GPU.  2(N-1)/N S per direction, all of it posted writes.
 //
-// Cross-GPU barriers use multimem.red.add on a per-CTA flag word that exists on every GPU, then
-// spin on the local copy (bounded: B200V_NVLS_TIMEOUT_MS, default 2000 — a peer that never
-// arrives yields B200V_E_TIMEOUT, never a hung GPU).  The count a CTA waits for lives in a small
+// A fifth kernel, hybrid, runs multimem and push on disjoint parts of one vector in one grid; it
+// measured no faster than either and stays selectable for A/B only.
+//
+// Cross-GPU barriers use multimem.red.release.add on a per-CTA flag word that exists on every GPU
+// (the release is the barrier's only fence), then spin on the local copy (bounded:
+// B200V_NVLS_TIMEOUT_MS, default 2000 — a peer that never arrives yields B200V_E_TIMEOUT, never a
+// hung GPU).  The count a CTA waits for lives in a small
 // per-GPU array (`epochs`) that only that CTA index touches, so kernels with different grids can
-// follow each other freely.  B200V_NVLS_ALGO=multimem|p2p|push|oneshot forces one kernel.
+// follow each other freely.  B200V_NVLS_ALGO=multimem|p2p|push|oneshot|hybrid forces one kernel.
 //
 // Everything from the CUDA driver API is resolved through cudaGetDriverEntryPoint, so the library
 // keeps having no link-time dependency on libcuda.
