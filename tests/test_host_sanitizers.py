@@ -39,6 +39,11 @@ def test_validator_scenarios_run_clean_under_asan_ubsan(san_fake, tmp_path):
         (1, dict(COMPONENT="cuda", FAKE_MODE="cudaerr", WITH_WAIT="true", B200V_MAX_RETRIES=2)),
         (1, dict(COMPONENT="cuda", B200V_INJECT_FAULT=49999)),
         (0, dict(COMPONENT="cuda", B200V_ELEMS=0)),
+        # the fan-out pipes, the start barrier, child rows, the whole-node line and the .prom file
+        (0, dict(COMPONENT="cuda", FAKE_NDEV=3, B200V_ELEMS=1 << 22, B200V_WRITE_PROM=1)),
+        (0, dict(COMPONENT="cuda", FAKE_NDEV=1, B200V_FANOUT_FORCE=1, B200V_FANOUT_HBM_LOG2=20)),
+        (1, dict(COMPONENT="cuda", FAKE_NDEV=3, FAKE_MODE="cudaerr", FAKE_FAIL_DEVICE=2, B200V_ELEMS=1 << 22)),
+        (0, dict(B200V_MODE="stream", B200V_GPUS=2, FAKE_NDEV=2, B200V_MIN_LOG2=18, B200V_MAX_LOG2=18)),
         (0, dict(COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=8)),
         (1, dict(COMPONENT="plugin", B200V_ALLOCATABLE_GPUS=0, B200V_PLUGIN_RETRIES=2)),
         (0, dict(COMPONENT="toolkit", B200V_NVIDIA_SMI="true")),
