@@ -1,7 +1,11 @@
 """CPU tests of the oracle: pins against the committed golden vectors, against SURVEY.md §8(c)'s
 recorded values, and against independent restatements (numpy, and a pure-Python glibc rand())."""
+import os
+
 import numpy as np
 import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def bits(a):
@@ -199,3 +203,29 @@ def test_threaded_vadd_matches_scalar(oracle):
     A = oracle.fill_hash(100003, 11)
     B = oracle.fill_hash(100003, 12)
     assert oracle.vadd(A, B, threads=5).tobytes() == oracle.vadd(A, B).tobytes()
+
+
+def test_committed_sweep_digests_are_what_the_oracle_computes(oracle):
+    """tests/golden/sweep_digests.json (bench.py's checker for the 2^30 and 2^32 rows of the STREAM
+    sweep) against the live oracle at the sizes that take a moment on the CPU, through the same
+    piecewise routine bench.py uses — so the committed file, the generator script and the bench's
+    own digest arithmetic cannot drift apart."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    with open(os.path.join(ROOT, "tests", "golden", "sweep_digests.json")) as f:
+        golden = json.load(f)
+    assert golden["seed"] == bench.SEED and golden["scalar"] == 3.0
+    assert {int(k) for k in golden["log2_n"]} >= set(bench.SWEEP_LOG2)
+    ops = [oracle.OP_COPY, oracle.OP_SCALE, oracle.OP_ADD, oracle.OP_TRIAD]
+    for lg in (18, 22, 24, 25):                      # below, at and above the 2^24-element piece size
+        if str(lg) not in golden["log2_n"]:
+            continue
+        got = bench.oracle_sweep_digests(oracle, lg, ops, 3.0)
+        want = [int(golden["log2_n"][str(lg)][name], 16) for name in ("copy", "scale", "add", "triad")]
+        assert got == want, lg
+    # the digest is position-sensitive: the same values one element later do not collide
+    x = oracle.fill_hash(1000, bench.SEED)
+    assert oracle.digest_from(x, 0) != oracle.digest_from(x, 1)
