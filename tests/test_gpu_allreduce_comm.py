@@ -147,6 +147,43 @@ def test_peer_kernels_add_in_rank_order(capi, gpu, algo, monkeypatch):
         assert got[r].tobytes() == want.tobytes(), "rank %d" % r
 
 
+def test_a_rank_that_never_arrives_times_out_instead_of_hanging(capi, gpu, monkeypatch):
+    """A health probe must not wedge a GPU.  Rank 0 starts an all-reduce that rank 1 never joins:
+    its kernel gives up after the bounded spin (200 ms here), the stream drains, and
+    b200v_nvls_comm_check reports B200V_E_TIMEOUT."""
+    import time
+
+    import torch
+    if gpu < 2:
+        pytest.skip("needs at least two GPUs")
+    monkeypatch.setenv("B200V_NVLS_TIMEOUT_MS", "200")
+    comms = [None, None]
+
+    def make(r):
+        torch.cuda.set_device(r)
+        try:
+            comms[r] = capi.NvlsComm(r, r, 2, "b200v-comm-timeout-%d" % os.getpid(), 1 << 20)
+        except capi.B200VError as e:
+            if e.code != capi.E_UNSUPPORTED:
+                raise
+    _run_ranks(2, make)
+    if comms[0] is None or comms[1] is None:
+        pytest.skip("no multicast support on this box")
+    try:
+        torch.cuda.set_device(0)
+        buf = torch.ones(4096, device="cuda:0")
+        t0 = time.time()
+        comms[0].allreduce(buf.data_ptr(), buf.numel())      # rank 1 stays away
+        with pytest.raises(capi.B200VError) as ei:
+            comms[0].check()
+        assert ei.value.code == capi.E_TIMEOUT
+        assert time.time() - t0 < 10.0                       # bounded: nowhere near a hang
+        torch.cuda.synchronize(0)                            # the GPU is still usable
+        assert float(torch.ones(8, device="cuda:0").sum()) == 8.0
+    finally:
+        _run_ranks(2, lambda r: comms[r].close())
+
+
 def test_nvls_comm_rejects_what_it_cannot_hold(capi, gpu):
     import torch
     with pytest.raises(capi.B200VError) as ei:
